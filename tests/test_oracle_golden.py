@@ -1,0 +1,156 @@
+"""Pins the CPU oracle against every golden vector / known-answer test the reference holds for the
+hot path.  CPU only."""
+import zlib
+
+import numpy as np
+import pytest
+
+import pyoracle as po
+from conftest import ALIST_300, ALIST_100_23, ALIST_100_27
+
+
+def test_crc32_matches_zlib():
+    # lib/dtl/crc_util.cc:23: crc(32, 0x04C11DB7, 0xFFFFFFFF, 0xFFFFFFFF, true, true) == zlib CRC-32
+    rng = np.random.default_rng(1)
+    for n in (0, 1, 9, 243, 1000):
+        d = rng.integers(0, 256, n, dtype=np.uint8)
+        assert po.crc32(d) == zlib.crc32(d.tobytes())
+    assert po.crc32(np.frombuffer(b"123456789", dtype=np.uint8)) == 0xCBF43926
+
+
+def test_frame_pack_golden_bytes():
+    # python/dtl/qa_ofdm_adaptive_frame_pack_bb.py:39-42
+    p1 = [0b101] + [0b111] * 4 + [0b001] + 11 * [0b000]
+    p2 = [0b01] + [0b11] * 7 + 16 * [0b00]
+    out1, _ = po.frame_pack(po.PSK8, p1)
+    out2, _ = po.frame_pack(po.QPSK, p2)
+    assert list(out1) + list(out2) == [0b11111101, 0b11111111, 0b11111101, 0b11111111]
+
+
+def test_constellation_metric_golden():
+    # python/dtl/qa_ofdm_adaptive_constellation_metric_vcvf.py:86
+    a, b = po.points(po.PSK8)[0], po.points(po.BPSK)[0]
+    assert abs(abs(a - b) ** 2 / po.min_dist2(po.PSK8) - 6.568538665771484) < 1e-6
+
+
+def test_feedback_decision_sequence():
+    # python/dtl/qa_ofdm_adaptive_feedback_decision.py:47-59
+    th = 3
+    mcs = [(2.2250738585072014e-308, (po.BPSK, 0)), (13, (po.QPSK, 0)), (18, (po.PSK8, 0)), (23, (po.QAM16, 0))]
+    fd = po.FeedbackDecision(1, th, mcs, 1)
+    seq = ((th + 1) * 3 - 1) * [27] + ((th + 1) * 3 - 1) * [14.5]
+    expected = (th * [po.QPSK] + (th + 1) * [po.PSK8] + (th + 1) * [po.QAM16] + th * [po.QAM16] +
+                (th + 1) * [po.PSK8] + (th + 1) * [po.QPSK])
+    assert [fd.get_feedback(s)[0] for s in seq] == expected
+
+
+HDR_NOFEC = [
+    0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 1, 0, 0, 1, 0, 1, 1, 1, 1, 1, 1, 0, 1, 1, 0, 0,
+    0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 0, 0, 0, 0, 0, 0, 1, 0, 0, 1, 1, 0, 1, 0, 1, 0, 1, 1, 0, 0, 0, 1,
+    0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 1, 1, 1, 1, 0, 0, 0, 1, 0, 1, 0]
+HDR_FEC = [
+    0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,1,0,0,0,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,1,1,1,1,1,1,1,1,0,0,0,0,1,0,0,0,0,1,0,1,0,1,0,1,0,0,0,0,0,0,0,0,0,1,1,1,0,0,0,1,1,0,1,0,1,0,1,0,
+    0,1,0,0,0,0,0,0,0,0,0,0,1,0,0,0,0,0,0,0,0,0,0,0,1,1,0,0,0,0,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,1,1,0,0,0,1,1,1,0,1,0,0,1,
+    0,0,1,0,0,0,0,0,0,0,0,0,0,1,0,0,0,0,0,0,0,0,0,0,0,1,0,0,0,0,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,1,0,0,0,1,0,1,0,1,0,1,0,0,0,0,0,0,0,0,0,1,1,0,0,0,0,0,1,0,0,1,1,1,0,1]
+
+
+def test_packet_header_golden_no_fec():
+    # python/dtl/qa_ofdm_adaptive_packet_header.py:73-149 (CRC-16 + field layout, 48-bit header)
+    h = po.PacketHeader(48, 1, False)
+    m = np.zeros(1, dtype=po.frame_meta_dtype)
+    bits = []
+    for i, (plen, c) in enumerate(((4, 4), (2, 3), (4, 2))):
+        m["payload_len"], m["constellation"] = plen, c
+        b = h.format(m[0])
+        bits += list(b)
+        ok, pm, fc, _ = po.PacketHeader(48, 1, False).parse(b)
+        assert ok and pm["payload_len"] == plen and pm["constellation"] == c and pm["frame_no"] == i
+        assert pm["packet_len"] == plen * 8 // c + int(plen * 8 % c > 0) and fc == 0
+    assert bits == HDR_NOFEC
+
+
+def test_packet_header_golden_fec():
+    # python/dtl/qa_ofdm_adaptive_packet_header.py:151-262 (96-bit header with the FEC fields)
+    h = po.PacketHeader(96, 1, True)
+    m = np.zeros(1, dtype=po.frame_meta_dtype)
+    bits = []
+    fec = ((1, 0xff, 1, 0xaa), (1, 0, 0, 0), (1, 0, 2, 0xaa))
+    for (plen, c), f in zip(((4, 4), (2, 3), (4, 2)), fec):
+        m["payload_len"], m["constellation"] = plen, c
+        m["tb_no"], m["tb_offset"], m["fec_id"], m["tb_payload"] = f
+        b = h.format(m[0])
+        bits += list(b)
+        ok, pm, _, _ = po.PacketHeader(96, 1, True).parse(b)
+        assert ok and (pm["tb_no"], pm["tb_offset"], pm["fec_id"], pm["tb_payload"]) == f
+    assert bits == HDR_FEC
+    bad = np.array(HDR_FEC[:96], dtype=np.uint8)
+    bad[3] ^= 1
+    assert not po.PacketHeader(96, 1, True).parse(bad)[0]       # CRC-16 drop, packet_header.cc:261-267
+
+
+@pytest.mark.parametrize("path,n,m,k,edges", [(ALIST_300, 300, 148, 152, 888), (ALIST_100_23, 100, 77, 23, 385),
+                                              (ALIST_100_27, 100, 73, 27, 292)])
+def test_alist_dimensions_and_encoder(path, n, m, k, edges):
+    # fixture facts from SURVEY.md section 4 (edge counts, GF(2) ranks)
+    cfg = po.Config(alists=[path])
+    info = cfg.code_info(1)
+    assert (info["N"], info["M"], info["K"], info["edges"]) == (n, m, k, edges)
+    assert sorted(info["permute"]) == list(range(n))
+    rng = np.random.default_rng(3)
+    data = rng.integers(0, 2, (16, k), dtype=np.uint8)
+    cw = cfg.ldpc_encode(1, data)
+    assert np.array_equal(cw[:, n - k:], data)                  # wire order = [parity | data], ldpc_enc.cc:65-67
+    assert all(cfg.ldpc_syndrome(1, c) == 0 for c in cw)
+    # noiseless round trip: decoder returns at the initial hard-decision syndrome check (nit == 0)
+    llr = np.where(cw == 1, 10.0, -10.0).astype(np.float32)     # positive LLR = bit 1 (soft_cf), ldpc_dec negates
+    out, nit = cfg.ldpc_decode(1, llr)
+    assert np.array_equal(out, data) and not nit.any()
+
+
+def test_map_decide_identity_and_qa_vector():
+    # python/dtl/qa_ofdm_adaptive_chunks_to_symbols_bc.py:39-63
+    for c in (po.BPSK, po.QPSK, po.PSK8, po.QAM16, po.QAM64, po.QAM256):
+        idx = np.arange(1 << po.bps(c), dtype=np.uint8)
+        assert np.array_equal(po.decide(c, po.map_chunks(c, idx)), idx)
+    v = np.array([0, 1, 2, 3, 3, 2, 1, 0], dtype=np.uint8)
+    assert np.array_equal(po.decide(po.QPSK, po.map_chunks(po.QPSK, v)), v)
+    assert np.allclose(np.abs(po.points(po.QPSK)), 0.5, atol=1e-6)      # lib/dtl/constellation.cc:18-24
+    for c in (po.BPSK, po.PSK8, po.QAM16, po.QAM64, po.QAM256):
+        assert abs(np.mean(np.abs(po.points(c)) ** 2) - 1.0) < 1e-5
+
+
+def test_soft_dec_sign_and_order():
+    # soft_cf_impl.cc:143-148: LSB-first after the reverse; positive LLR = bit 1
+    for c in (po.BPSK, po.QPSK, po.PSK8, po.QAM16, po.QAM64):
+        b = po.bps(c)
+        idx = np.arange(1 << b, dtype=np.uint8)
+        llr = po.soft_dec(c, po.map_chunks(c, idx), 0.05).reshape(-1, b)
+        bits = (idx[:, None] >> np.arange(b)[None, :]) & 1
+        assert np.array_equal(llr > 0, bits == 1)
+    # default sigma 0.001 (soft_cf_impl.cc:89) saturates to +-inf on noiseless symbols
+    llr = po.soft_dec(po.QPSK, po.points(po.QPSK), 0.001)
+    assert np.all(np.isinf(llr))
+
+
+def test_equalizer_qa_scenario():
+    # python/dtl/qa_ofdm_adaptive_frame_equalizer_vcvc.py:64-165 (fft_len 8, 4 symbols, one pilot symbol row)
+    rng = np.random.default_rng(11)
+    for c in (po.QPSK, po.PSK8):
+        pts = po.points(c)
+        tx_data = [-1, -1, 1, 2, -1, 3, 0, -1, -1, -1, 0, 2, -1, 2, 0, -1, -1, -1, 3, 0, -1, 1, 0, -1, -1, -1, 1, 1, -1, 0, 2, -1]
+        tx = np.array([pts[x] if x != -1 else 0 for x in tx_data], dtype=np.complex64)
+        cfg = po.Config(fft_len=8, cp_len=0, frame_len=4, occupied=[1, 2, 6, 7], pilots=[],
+                        pilot_carrier_sets=[(), (), (1, 2, 6, 7), ()],
+                        pilot_symbol_sets=[[], [], [pts[x] for x in (1, 0, 3, 0)], []],
+                        mcs=[(2.2250738585072014e-308, (po.BPSK, 0)), (13, (po.QPSK, 0)), (18, (po.PSK8, 0)), (23, (po.QAM16, 0))])
+        chan = np.array([0, 0, 1, 1, 0, 1, 1, 0] * 2 + [0, 0, 1j, 1j, 0, 1j, 1j, 0] * 2, dtype=np.complex128)
+        chan[8:16] = chan[0:8] * np.exp(1j * .1 * np.pi * (rng.random(8) - .5))
+        rx = (tx * chan + np.where(tx != 0, rng.normal(0, 0.001, 32), 0)).astype(np.complex64)
+        feq = po.FrameEqualizer(cfg, symbols_skipped=0, alpha=0.01)
+        m = np.zeros(1, dtype=po.frame_meta_dtype)
+        m["constellation"], m["payload_len"] = c, 1
+        n, hard, soft, res, _ = feq.work(rx, chan[:8].astype(np.complex64), m[0])
+        assert n == 4
+        dec = [int(po.decide(c, hard[i:i + 1])[0]) if hard[i] != 0 else -1 for i in range(32)]
+        assert dec == tx_data
+        assert (res["fb_cnst"], res["fb_fec"]) == (po.BPSK, 0)      # :162-165 feedback {constellation: 1, fec: 0}
