@@ -1,0 +1,89 @@
+// ctx.hpp -- internal definitions shared by the host side and the kernels of libdtl_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/dtl_b200.h"
+
+namespace dtl {
+
+// ---- device-side tables -----------------------------------------------------------------------------
+// Constellation point tables live in global memory (divergent index -> __ldg, not __constant__).
+struct CnstDev {
+    const float2* points;       // concatenated, see off[]
+    const float2* inv_points;   // 1/point (fp32 of the double quotient)
+    int off[DTL_CNST_MAX + 2];  // start of constellation c in points[]
+    int bps[DTL_CNST_MAX + 1];
+    float level[DTL_CNST_MAX + 1], inv2l[DTL_CNST_MAX + 1];   // square-QAM level, 1/(2*level)
+};
+
+// Carrier plan of the payload equaliser + serialiser, in shifted-bin coordinates.
+struct PlanDev {
+    int N, L, cap;               // fft_len, payload symbols per frame, frame capacity (data symbols)
+    int npc, nps, nocc;          // pilot-carrier sets, pilot-symbol sets, occupied sets
+    int pcs0;                    // symbols_skipped % npc
+    int symbols_skipped;
+    int npil_frame;              // pilots per frame (pilot_prefix[L])
+    int max_off;                 // |carrier offset| bound of phase_tab
+    float alpha, oma;            // alpha, 1 - alpha (fp32)
+    const uint8_t* occupied;     // [N]
+    const uint8_t* pilot_mask;   // [npc][N]
+    const uint16_t* pilot_rank;  // [npc][N] rank of bin among the pilots of the set
+    const int* pilot_prefix;     // [L+1] pilots before symbol i
+    const float2* pilot_sym;     // [nps][N]
+    const float2* pilot_inv;     // [nps][N]
+    const int16_t* ser_pos;      // [nocc][N] serialiser position of bin in set, -1 = not in set
+    const int* ser_base;         // [L+1] serialised symbols before OFDM symbol i
+    const float2* phase_tab;     // [2*max_off+1][L+1]: per-symbol correction i<L, taps rotation at L
+};
+
+// One LDPC code (gr-fec alist + cldpc permutation) in device memory.
+struct CodeDev {
+    int n, m, k, rank, edges, max_row, max_col;
+    const uint16_t* row_ptr;     // [m+1] edges are stored check-major (mlist order)
+    const uint16_t* row_var;     // [edges] variable of edge
+    const uint16_t* col_ptr;     // [n+1]
+    const uint16_t* col_edge;    // [edges] edge ids of variable v in nlist order
+    const uint16_t* permute;     // [n]
+};
+
+// Per-stream receiver state that survives between calls.
+struct StreamState {
+    // ofdm_adaptive_feedback_decision
+    int fb_last, fb_next, fb_counter;
+    // frame equaliser block counters
+    int expected_frame_no; int lost_frames; int frames_count;
+    // tb_decoder
+    int tb_number, tb_payload_len, have_info;
+    int info_fec, info_tb_payload, info_tb_number;
+    int carry_len;               // LLRs of the TB in flight held in the carry buffer
+    int buf_idx;                 // tb_decoder's d_buf_idx (capacity check only)
+    int frame_index;             // frames seen by the FEC decoder
+};
+
+struct TbSeg { int src; int start; int len; };   // src: -1 = carry buffer, else frame index in this call
+#define DTL_TB_MAXSEG 6
+struct TbDesc {
+    int stream, fec_id, ncws, payload_len, tb_no, frame_index;
+    int nseg; TbSeg seg[DTL_TB_MAXSEG];
+    int cw_first;                // index of the first codeword work item
+    long long bit_base;          // offset of the TB's bits in the bit scratch
+};
+
+struct Code {                    // host copy
+    int n = 0, m = 0, k = 0, rank = 0, edges = 0, max_row = 0, max_col = 0;
+    std::vector<std::vector<int>> nlist, mlist;
+    std::vector<int> permute;
+    std::vector<std::vector<uint8_t>> P;   // rank x k parity part (for the TX-side encoder)
+    CodeDev dev{};
+    std::string path;
+};
+
+bool load_alist(const std::string& path, Code& c, std::string& err);
+
+// host constellation tables (lib/dtl/ofdm_adaptive_utils.cc:41-70, lib/dtl/constellation.cc:18-24)
+int cnst_bps(int c);
+void cnst_points(int c, std::vector<float2>& pts, std::vector<float2>& inv, float* level, float* inv2l);
+
+} // namespace dtl

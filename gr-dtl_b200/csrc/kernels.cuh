@@ -1,0 +1,90 @@
+// kernels.cuh -- kernel parameter blocks and launcher prototypes (internal).
+#pragma once
+#include "ctx.hpp"
+
+namespace dtl {
+
+__host__ __device__ inline int log2n_of(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
+
+// ---- stage 5 ------------------------------------------------------------------------------------------
+struct TxParams {
+    int N, cp, H, L, cap, nocc, hdr_stride;
+    long long n_frames;
+    const uint8_t* hdr_bits; const uint8_t* chunks; const dtl_frame_meta* meta;
+    const float2* sync1; const float2* sync2;      // [N] shifted layout
+    const int16_t* ser_pos;                        // [nocc][N]
+    const int* tx_base;                            // [H+L+1] data symbols before OFDM data symbol s
+    const uint8_t* tx_pil_mask;                    // [H+L][N]
+    const float2* tx_pil_val;                      // [H+L][N]
+    const float2* tw; CnstDev cn; float2* iq;
+};
+
+// ---- stages 2+3 -----------------------------------------------------------------------------------------
+struct EqParams {
+    PlanDev pl; CnstDev cn;
+    const float2* freq; const float2* taps; const dtl_frame_meta* meta;
+    long long n_frames;
+    float2* out_hard; float2* out_soft; float2* taps_out;
+    dtl_frame_result* res;                         // snr_db, noise, emitted filled here
+    float* llr; int llr_stride; int* n_llr;
+    uint8_t* bytes; int bytes_stride; int* nbytes; int* crc_ok;
+    const uint32_t* crc_table;                     // [256] reflected CRC-32
+    int* err;                                      // device error word (bit 0: bad constellation)
+    // fused stage 1 (in_kind 0): time-domain IQ instead of freq
+    const float2* iq; int frame_samples, cp, sym0; const float2* tw;
+};
+
+// ---- per-stream sequential bookkeeping ------------------------------------------------------------------
+struct StreamParams {
+    StreamState* st; int n_streams, F;
+    const dtl_frame_meta* meta; dtl_frame_result* res;
+    int n_mcs; const double* mcs_snr; const int* mcs_cnst; const int* mcs_fec; double hysteresis; int decision_th;
+};
+
+// ---- stage 4 ------------------------------------------------------------------------------------------------
+struct FecParams {
+    StreamState* st; int n_streams, F;
+    const dtl_frame_meta* meta;
+    const float* llr; int llr_stride;
+    float* carry; int carry_cap;                   // [S][carry_cap]
+    int n_codes; const CodeDev* codes;             // [n_codes+1], entry 0 unused
+    int cap; int bps_tab[DTL_CNST_MAX + 1];
+    int max_tb;                                    // tb_decoder capacity (max_n * ncws(max_bps))
+    TbDesc* tbs; int tb_slots;                     // [S][tb_slots] released TBs of this call
+    TbDesc* pend;                                  // [S] segments of the TB still in flight
+    dtl_tb_result* tres;                           // [S][tb_slots]
+    int* tb_count;                                 // [S]
+    int* tb_list;                                  // compact list of released TB indices
+    int* cw_tb; int cw_cap;                        // codeword work list: TB index of work item
+    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs
+    unsigned long long* bits_used;                 // bump allocator of the bit scratch
+    uint8_t* bits; long long bits_cap;             // decoded TB bits, one byte per bit, then packed in place
+    int* cw_nit;                                   // [cw_cap]
+    int max_it; double sigma2; int mode; int warp_bytes;
+    // outputs
+    uint8_t* bytes; int bytes_cap; int* nbytes; dtl_tb_result* tb_out; int tb_cap; int* ntbs;
+    const uint32_t* crc_table; int* err;
+};
+
+struct LdpcParams {                                // stand-alone fec_dec::decode batches
+    CodeDev code; const float* llr; long long count; uint8_t* bits; int* nit; int max_it; double sigma2; int mode;
+    int* cursor; int warp_bytes;
+};
+
+struct DemapParams {
+    CnstDev cn; const float2* syms; int stride_syms; const dtl_frame_meta* meta; const double* noise;
+    long long n_frames; float* llr; int llr_stride; uint8_t* chunks; const uint8_t* in_chunks; float2* out_syms; int mode;
+};
+
+cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long long n_sym, int syms_per_frame,
+                           long long in_frame_stride, int in_sym0, int in_sym_stride, int in_skip, int N, const float2* tw);
+cudaError_t launch_fft_inv(cudaStream_t st, const float2* in, float2* out, long long n_sym, int N, const float2* tw);
+cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p);
+cudaError_t launch_eq(cudaStream_t st, const EqParams& p);
+cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches);
+size_t ldpc_warp_bytes(int n, int edges);
+cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
+cudaError_t launch_demap(cudaStream_t st, const DemapParams& p);   // mode 0 soft, 1 hard, 2 map
+
+} // namespace dtl

@@ -1,0 +1,332 @@
+// kernels_fec.cu -- stage 4: transport-block reassembly, LDPC belief-propagation decode, CRC-32, byte packing.
+//
+// Replaces (one frame / one codeword at a time in the reference):
+//   ofdm_adaptive_fec_decoder_impl::general_work  lib/dtl/ofdm_adaptive_fec_decoder_impl.cc:80-217
+//   make_fec_info / compute_tb_len                lib/dtl/fec_utils.cc:60-121
+//   tb_decoder::process_frame / decode            lib/dtl/tb_decoder.cc:32-195
+//   ldpc_dec::decode -> gr-fec awgn_bp::decode    lib/dtl/ldpc_dec.cc:62-71
+//   ofdm_adaptive_fec_pack_bb                     lib/dtl/ofdm_adaptive_fec_pack_bb_impl.cc:48-69
+//
+// Pipeline of one call (all on the handle's stream, nothing returns to the host in between):
+//   1. tb_plan_kernel     one thread per stream replays tb_decoder's frame-by-frame state machine on the
+//                         frame tags only, emitting for every released transport block (TB) the list of LLR
+//                         segments it is made of (carry buffer from earlier calls + ranges of this call's
+//                         frames) and one work item per codeword.
+//   2. ldpc_tb_kernel     persistent grid (CTAs = SMs x residency); each WARP pulls codeword work items from
+//                         a device counter, gathers its n LLRs (shortened positions = -15, tb_decoder.cc:145),
+//                         applies cldpc's column permutation, and decodes with messages in shared memory;
+//                         syndrome checks are warp votes, so a warp leaves as soon as its word converges.
+//   3. tb_finish_kernel   one warp per TB: bits -> bytes LSB-first (ballot), CRC-32 verify, mean iterations.
+//   4. tb_gather_kernel   one warp per stream: CRC-passing TBs' payload bytes concatenated in release order.
+//   5. carry_save_kernel  LLRs of the TB still in flight move to the per-stream carry buffer.
+//
+// Decoder flavours: DTL_LDPC_REFERENCE is gr-fec's awgn_bp restated operation by operation (flooding
+// sum-product on likelihood ratios, IEEE double, products in alist order) so payload bits AND iteration
+// counts match the reference; DTL_LDPC_LAYERED is a layered normalised min-sum in fp32 (throughput mode).
+#include "kernels.cuh"
+
+namespace dtl {
+
+#define ERR_TAGS 4
+#define ERR_FEC_TAGS 8
+#define ERR_TB_SLOTS 16
+#define ERR_CW_CAP 32
+#define ERR_BITS_CAP 64
+#define ERR_TB_META 128
+#define ERR_SEGS 256
+#define ERR_CARRY 512
+
+__device__ __forceinline__ int tb_ncws(int cw_len, int frame_len) { return frame_len > cw_len ? 1 + frame_len / cw_len : 1; }
+
+struct Rcv { TbSeg seg[DTL_TB_MAXSEG]; int nseg; int len; bool bad; };
+__device__ __forceinline__ void rcv_clear(Rcv& r) { r.nseg = 0; r.len = 0; r.bad = false; }
+__device__ __forceinline__ void rcv_push(Rcv& r, int src, int start, int len)
+{
+    if (len <= 0) return;
+    if (r.nseg == DTL_TB_MAXSEG) { r.bad = true; return; }
+    r.seg[r.nseg].src = src; r.seg[r.nseg].start = start; r.seg[r.nseg].len = len;
+    r.nseg++; r.len += len;
+}
+
+__global__ void tb_plan_kernel(FecParams p)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= p.n_streams) return;
+    StreamState st = p.st[s];
+    Rcv rcv; rcv_clear(rcv);
+    if (st.carry_len > 0) rcv_push(rcv, -1, 0, st.carry_len);
+    int ntb = 0, err = 0;
+
+    auto release = [&](int fec_id, int ncws, int payload_len, int tb_no, int frame_index) {
+        const CodeDev& c = p.codes[fec_id];
+        if (rcv.bad) { err |= ERR_SEGS; return; }
+        if (payload_len < 0 || payload_len > ncws * c.k) { err |= ERR_TB_META; return; }
+        if (ntb >= p.tb_slots) { err |= ERR_TB_SLOTS; return; }
+        const int first = atomicAdd(&p.cnt[0], ncws);
+        if (first + ncws > p.cw_cap) { err |= ERR_CW_CAP; return; }
+        const long long bit_base = (long long)atomicAdd(p.bits_used, (unsigned long long)((payload_len + 3) & ~3));
+        if (bit_base + payload_len > p.bits_cap) { err |= ERR_BITS_CAP; return; }
+        const int gi = s * p.tb_slots + ntb;
+        TbDesc& d = p.tbs[gi];
+        d.stream = s; d.fec_id = fec_id; d.ncws = ncws; d.payload_len = payload_len; d.tb_no = tb_no;
+        d.frame_index = frame_index; d.nseg = rcv.nseg; d.cw_first = first; d.bit_base = bit_base;
+        for (int i = 0; i < rcv.nseg; i++) d.seg[i] = rcv.seg[i];
+        for (int i = 0; i < ncws; i++) p.cw_tb[first + i] = gi;
+        p.tb_list[atomicAdd(&p.cnt[2], 1)] = gi;
+        ntb++;
+    };
+
+    for (int j = 0; j < p.F; j++) {
+        const dtl_frame_meta m = p.meta[(long long)s * p.F + j];
+        if (m.payload_len == 0) continue;                                   // frame not emitted / empty (:141-143)
+        const int bps = (m.constellation >= 1 && m.constellation <= DTL_CNST_MAX) ? p.bps_tab[m.constellation] : 0;
+        if (!bps) { err |= ERR_TAGS; continue; }                            // "Tags missing" (:121-126)
+        if (m.fec_id < 1 || m.fec_id > p.n_codes) { err |= ERR_FEC_TAGS; continue; }   // "FEC tags missing" (:136-138)
+        const int frame_index = st.frame_index++;
+        const CodeDev& fc = p.codes[m.fec_id];
+        const int fpl = 8 * m.payload_len, tb_off = 8 * m.tb_offset;       // :147
+        const int frame_len = 8 * ((p.cap * bps + 7) / 8);
+        if (m.tb_no == st.tb_number) {                                      // tb_decoder.cc:57-70
+            if (st.buf_idx + fpl > 2 * p.max_tb) { err |= ERR_CARRY; continue; }
+            rcv_push(rcv, j, 0, fpl);
+            st.buf_idx += fpl;
+            const int ncws = tb_ncws(p.codes[st.info_fec].n, frame_len);
+            const int expected = (fc.n - fc.k) * ncws + m.tb_payload;
+            if (rcv.len >= expected) {
+                release(st.info_fec, ncws, st.info_tb_payload, m.tb_no, frame_index);
+                st.buf_idx = 0; rcv_clear(rcv);
+            }
+        } else if (rcv.len == 0 && tb_off == fpl) {                         // :75-89
+            st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
+            st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
+            rcv_clear(rcv);
+            rcv_push(rcv, j, 0, tb_off);
+            release(m.fec_id, tb_ncws(fc.n, frame_len), m.tb_payload, m.tb_no, frame_index);
+            rcv_clear(rcv);
+        } else {                                                            // :92-133
+            if (tb_off > 0) rcv_push(rcv, j, 0, tb_off);
+            if (rcv.len > 0 && st.have_info)
+                release(st.info_fec, tb_ncws(p.codes[st.info_fec].n, frame_len), st.info_tb_payload, st.info_tb_number,
+                        frame_index);
+            st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
+            st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
+            rcv_clear(rcv);
+            int extra = 0;
+            if (tb_off % bps) extra = bps - tb_off % bps;
+            const int new_off = tb_off ? tb_off + extra : 0;
+            rcv_push(rcv, j, new_off, fpl + extra - new_off);
+            st.buf_idx += fpl - tb_off;
+            const int ncws = tb_ncws(fc.n, frame_len);
+            const int tb_size = 8 * ((ncws * (fc.n - fc.k) + m.tb_payload + 7) / 8);
+            if (fpl - tb_off == tb_size) {
+                release(m.fec_id, ncws, m.tb_payload, m.tb_no, frame_index);
+                st.buf_idx = 0; rcv_clear(rcv);
+            }
+        }
+    }
+    // what is left belongs to the TB in flight: carry_save_kernel moves it to the carry buffer
+    TbDesc& pd = p.pend[s];
+    pd.nseg = rcv.nseg; pd.stream = s;
+    for (int i = 0; i < rcv.nseg; i++) pd.seg[i] = rcv.seg[i];
+    if (rcv.bad) err |= ERR_SEGS;
+    if (rcv.len > p.carry_cap) { err |= ERR_CARRY; pd.nseg = 0; st.carry_len = 0; }
+    else st.carry_len = rcv.len;
+    p.tb_count[s] = ntb;
+    p.st[s] = st;
+    if (err) atomicOr(p.err, err);
+}
+
+// LLR number `idx` of a TB's receive buffer; reads past the received length return 0 (erasure).
+__device__ __forceinline__ float rcv_at(const TbDesc& d, int idx, const FecParams& p)
+{
+    int base = 0;
+    for (int i = 0; i < d.nseg; i++) {
+        const TbSeg sg = d.seg[i];
+        if (idx < base + sg.len) {
+            const int o = sg.start + (idx - base);
+            if (sg.src < 0) return p.carry[(size_t)d.stream * p.carry_cap + o];
+            return __ldcs(&p.llr[((size_t)d.stream * p.F + sg.src) * p.llr_stride + o]);
+        }
+        base += sg.len;
+    }
+    return 0.0f;
+}
+
+// ---- awgn_bp::decode for one codeword per warp ---------------------------------------------------------------
+// Shared memory per warp: msg[edges] double (Q and R share storage: a check overwrites its Q's with R's, a
+// variable overwrites its R's with Q's), lr0[n] double (channel likelihood ratios), rx[n] float, est[n] u8.
+struct WarpBuf { double* msg; double* lr0; float* rx; uint8_t* est; };
+
+size_t ldpc_warp_bytes(int n, int edges)
+{
+    size_t b = (size_t)edges * 8 + (size_t)n * 8 + (size_t)n * 4 + (size_t)((n + 15) & ~15);
+    return (b + 15) & ~(size_t)15;
+}
+
+__device__ __forceinline__ bool syndrome_nonzero(const CodeDev& c, const uint8_t* est, int lane)
+{
+    bool bad = false;
+    for (int r = lane; r < c.m; r += 32) {
+        unsigned par = 0;
+        for (int e = c.row_ptr[r]; e < c.row_ptr[r + 1]; e++) par ^= est[c.row_var[e]];
+        bad |= (par & 1u) != 0;
+    }
+    return __any_sync(0xffffffffu, bad);
+}
+
+// rx[] (H column order, rx < 0 => bit 1) must be filled; returns the iteration count, est[] = decisions.
+__device__ int bp_reference(const CodeDev& c, const WarpBuf& w, int lane, int max_it, double sigma2)
+{
+    for (int v = lane; v < c.n; v += 32) w.est[v] = w.rx[v] < 0.f ? 1 : 0;          // compute_init_estimate
+    __syncwarp();
+    if (!syndrome_nonzero(c, w.est, lane)) return 0;
+    for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc + spa_initialize
+        const float m2 = -1 * 2 * w.rx[v];
+        const double lr = exp(__ddiv_rn((double)m2, sigma2));
+        w.lr0[v] = lr;
+        for (int q = c.col_ptr[v]; q < c.col_ptr[v + 1]; q++) w.msg[c.col_edge[q]] = lr;
+    }
+    __syncwarp();
+    int nit = 0;
+    while (nit < max_it) {
+        nit++;
+        for (int r = lane; r < c.m; r += 32) {                                         // update_chks
+            const int e0 = c.row_ptr[r], e1 = c.row_ptr[r + 1];
+            double prod = 1.0;
+            for (int e = e0; e < e1; e++)
+                prod = __dmul_rn(prod, __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0));
+            for (int e = e0; e < e1; e++) {
+                const double t = __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0);
+                const double pp = __ddiv_rn(prod, t);
+                w.msg[e] = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
+            }
+        }
+        __syncwarp();
+        for (int v = lane; v < c.n; v += 32) {                                         // update_vars + decision
+            const int q0 = c.col_ptr[v], q1 = c.col_ptr[v + 1];
+            double sacc = w.lr0[v];
+            for (int q = q0; q < q1; q++) sacc = __dmul_rn(sacc, w.msg[c.col_edge[q]]);
+            for (int q = q0; q < q1; q++) { const int e = c.col_edge[q]; w.msg[e] = __ddiv_rn(sacc, w.msg[e]); }
+            w.est[v] = sacc > 1.0 ? 1 : 0;
+        }
+        __syncwarp();
+        if (!syndrome_nonzero(c, w.est, lane)) break;
+    }
+    return nit;
+}
+
+// Layered normalised min-sum (fp32, LLR domain, rx > 0 => bit 0): check rows are processed in order,
+// each lane owning whole rows of a 32-row layer group is not conflict-free for arbitrary alists, so rows are
+// processed one at a time by the lanes of the warp cooperating over the row's edges (row weight <= 32).
+__device__ int bp_layered(const CodeDev& c, const WarpBuf& w, int lane, int max_it)
+{
+    float* post = (float*)w.lr0;                  // posterior LLR per variable
+    float* cmsg = (float*)w.msg;                  // check->variable message per edge
+    for (int v = lane; v < c.n; v += 32) { post[v] = w.rx[v]; w.est[v] = w.rx[v] < 0.f ? 1 : 0; }
+    for (int e = lane; e < c.edges; e += 32) cmsg[e] = 0.f;
+    __syncwarp();
+    if (!syndrome_nonzero(c, w.est, lane)) return 0;
+    const float norm = 0.8125f;
+    int nit = 0;
+    while (nit < max_it) {
+        nit++;
+        for (int r = 0; r < c.m; r++) {
+            const int e0 = c.row_ptr[r], deg = c.row_ptr[r + 1] - e0;
+            float q = 1e30f; int v = 0; float old = 0.f;
+            if (lane < deg) { v = c.row_var[e0 + lane]; old = cmsg[e0 + lane]; q = post[v] - old; }
+            float a = fabsf(q);
+            unsigned sgn = __ballot_sync(0xffffffffu, lane < deg && q < 0.f);
+            float m1 = a; int arg = lane;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                const float om = __shfl_xor_sync(0xffffffffu, m1, o); const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+                if (om < m1 || (om == m1 && oa < arg)) { m1 = om; arg = oa; }
+            }
+            float a2 = lane == arg ? 1e30f : a, m2 = a2;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) m2 = fminf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+            if (lane < deg) {
+                const float mag = norm * (lane == arg ? m2 : m1);
+                const bool neg = ((__popc(sgn) & 1) != 0) != (q < 0.f);
+                const float nm = neg ? -mag : mag;
+                cmsg[e0 + lane] = nm;
+                post[v] = q + nm;
+            }
+            __syncwarp();
+        }
+        for (int v = lane; v < c.n; v += 32) w.est[v] = post[v] < 0.f ? 1 : 0;
+        __syncwarp();
+        if (!syndrome_nonzero(c, w.est, lane)) break;
+    }
+    return nit;
+}
+
+__device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int edges)
+{
+    WarpBuf w;
+    w.msg = (double*)base;
+    w.lr0 = (double*)(base + (size_t)edges * 8);
+    w.rx = (float*)(base + (size_t)edges * 8 + (size_t)n * 8);
+    w.est = (uint8_t*)(base + (size_t)edges * 8 + (size_t)n * 8 + (size_t)n * 4);
+    return w;
+}
+
+__global__ void __launch_bounds__(256) ldpc_tb_kernel(FecParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned char* base = sm + (size_t)wid * p.warp_bytes;
+    const int total = min(p.cnt[0], p.cw_cap);
+    for (;;) {
+        int it = 0;
+        if (lane == 0) it = atomicAdd(&p.cnt[1], 1);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= total) break;
+        const TbDesc& d = p.tbs[p.cw_tb[it]];
+        const CodeDev& c = p.codes[d.fec_id];
+        const int ci = it - d.cw_first, ncheck = c.n - c.k;
+        // codeword geometry inside the TB (tb_decoder.cc:161-183)
+        int rem = d.payload_len, rcv_idx = 0, d_idx = 0, k_ = 0;
+        for (int i = 0; i <= ci; i++) {
+            k_ = rem / (d.ncws - i);
+            if (rem % (d.ncws - i)) ++k_;
+            if (i < ci) { rem -= k_; rcv_idx += ncheck + k_; d_idx += k_; }
+        }
+        const WarpBuf w = carve(base, c.n, c.edges);
+        for (int q = lane; q < c.n; q += 32) {                              // ldpc_dec.cc:64-66
+            const float v = q < ncheck + k_ ? rcv_at(d, rcv_idx + q, p) : -15.0f;
+            w.rx[c.permute[q]] = -1 * v;
+        }
+        __syncwarp();
+        const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered(c, w, lane, p.max_it)
+                                                   : bp_reference(c, w, lane, p.max_it, p.sigma2);
+        uint8_t* out = p.bits + d.bit_base + d_idx;
+        for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute[c.rank + q]];   // cldpc::get_systematic_bits
+        if (lane == 0) p.cw_nit[it] = nit;
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const CodeDev& c = p.code;
+    const WarpBuf w = carve(sm + (size_t)wid * p.warp_bytes, c.n, c.edges);
+    for (;;) {
+        long long it = 0;
+        if (lane == 0) it = atomicAdd(p.cursor, 1);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= p.count) break;
+        const float* in = p.llr + it * c.n;
+        for (int q = lane; q < c.n; q += 32) w.rx[c.permute[q]] = -1 * in[q];
+        __syncwarp();
+        const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered(c, w, lane, p.max_it)
+                                                   : bp_reference(c, w, lane, p.max_it, p.sigma2);
+        uint8_t* out = p.bits + it * c.k;
+        for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute[c.rank + q]];
+        if (lane == 0 && p.nit) p.nit[it] = nit;
+        __syncwarp();
+    }
+}
+

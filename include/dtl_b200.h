@@ -1,0 +1,230 @@
+/* dtl_b200.h -- C ABI of libdtl_b200.so: gr-dtl's adaptive-OFDM receive hot path (and the matching
+ * TX map/IFFT path) as hand-written CUDA kernels for sm_100a.
+ *
+ * This is the drop-in boundary: the GNU Radio block shims (gr-dtl_b200/gr_shim/, same block names,
+ * io signatures, stream tags and make() parameters as the reference) and the Python mirror
+ * (gr-dtl_b200/dtl_b200/) call ONLY these entry points.  Plain pointers and sizes, no C++/torch/GNU
+ * Radio types, no exceptions across the boundary: every call returns a dtl_status.
+ *
+ * Batching.  The reference's scheduler hands each block one tagged frame per work() call; here every
+ * call takes `n_streams x frames_per_stream` frames at once.  Frames are laid out stream-major,
+ * f = s * frames_per_stream + j; frames of one stream are consecutive in time.  The stream tags the
+ * reference reads on the first item of a frame travel as one `dtl_frame_meta` per frame, and the tags /
+ * messages it emits come back as one `dtl_frame_result` per frame (+ `dtl_tb_result` per transport block).
+ *
+ * Memory.  Every data pointer of a call is a HOST pointer when `mem == DTL_MEM_HOST` (the call stages
+ * through pinned buffers, copies in, runs, copies out and returns when the outputs are valid) or a
+ * DEVICE pointer of the handle's device when `mem == DTL_MEM_DEVICE` (the call only enqueues kernels
+ * on the handle's stream; use dtl_b200_sync before reading).  Output pointers may be NULL = not wanted.
+ *
+ * Threading: a handle is not thread-safe (GNU Radio never re-enters work() of one block instance);
+ * distinct handles are independent and own one CUDA stream each.
+ *
+ * Each entry point cites the reference interface (file:line under mihaipstef/gr-dtl) it replaces.
+ */
+#ifndef DTL_B200_H
+#define DTL_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DTL_B200_ABI_VERSION 1
+
+typedef enum dtl_status {
+    DTL_OK = 0,
+    DTL_ERR_INVALID_ARG = 1,    /* std::invalid_argument in the reference (unknown constellation, ...) */
+    DTL_ERR_MISSING_TAG = 2,    /* "Missing constellation tag" / "Tags missing" / "FEC tags missing" */
+    DTL_ERR_CUDA = 3,           /* CUDA runtime failure; dtl_b200_last_error() has the text */
+    DTL_ERR_NO_DEVICE = 4,      /* no CUDA device: there is NO CPU fallback */
+    DTL_ERR_UNSUPPORTED = 5,    /* configuration outside what the kernels cover */
+    DTL_ERR_CAPACITY = 6,       /* an output buffer / internal table was too small */
+    DTL_ERR_IO = 7              /* alist file unreadable / malformed */
+} dtl_status;
+
+typedef enum dtl_mem { DTL_MEM_HOST = 0, DTL_MEM_DEVICE = 1 } dtl_mem;
+
+/* constellation_type_t, include/gnuradio/dtl/ofdm_adaptive_utils.h:22-28; 5 and 6 are extensions that
+ * still fit the 4-bit header field (lib/dtl/ofdm_adaptive_packet_header.cc:157,173). */
+enum { DTL_CNST_UNKNOWN = 0, DTL_CNST_BPSK = 1, DTL_CNST_QPSK = 2, DTL_CNST_PSK8 = 3, DTL_CNST_QAM16 = 4,
+       DTL_CNST_QAM64 = 5, DTL_CNST_QAM256 = 6, DTL_CNST_MAX = 6 };
+
+/* POD mirror of the stream tags on the first item of a frame
+ * (lib/dtl/ofdm_adaptive_utils.cc:23-39 key names; read at
+ *  lib/dtl/ofdm_adaptive_frame_equalizer_vcvc_impl.cc:114-150,
+ *  lib/dtl/ofdm_adaptive_constellation_soft_cf_impl.cc:84-111, lib/dtl/fec_utils.cc:60-102). */
+typedef struct dtl_frame_meta {
+    int32_t constellation;   /* "constellation_tag_key" */
+    int32_t carrier_offset;  /* "ofdm_sync_carr_offset" */
+    int32_t frame_no;        /* "frame_no" (mod 4096) */
+    int32_t payload_len;     /* "payload_length_key", bytes */
+    int32_t packet_len;      /* "packet_length": constellation symbols = ceil(payload*8/bps) */
+    int32_t fec_id;          /* "fec_key" (1-based; 0 = none) */
+    int32_t tb_no;           /* "fec_tb_key" */
+    int32_t tb_offset;       /* "fec_offset_key", bytes */
+    int32_t tb_payload;      /* "fec_tb_payload_key", bits */
+    int32_t reserved;
+} dtl_frame_meta;
+
+/* Tags / feedback message the frame equaliser emits per frame
+ * (lib/dtl/ofdm_adaptive_frame_equalizer_vcvc_impl.cc:196-251). */
+typedef struct dtl_frame_result {
+    double snr_db;           /* "estimated_snr_tag_key" */
+    double noise;            /* "noise_tag_key" (linear) */
+    int32_t fb_cnst;         /* "feedback_constellation_key" */
+    int32_t fb_fec;          /* "fec_feedback_key" */
+    int32_t emitted;         /* OFDM symbols emitted (0 when payload_len == 0, :218-254) */
+    int32_t lost_frames;     /* running lost-frame count of the stream (:124-138) */
+} dtl_frame_result;
+
+/* One decoded transport block (monitor message of lib/dtl/ofdm_adaptive_fec_decoder_impl.cc:184-196). */
+typedef struct dtl_tb_result {
+    int32_t tb_no, crc_ok, nbytes, avg_it, frame_index;
+} dtl_tb_result;
+
+/* LDPC decoder flavour.  REFERENCE = gr-fec awgn_bp restated: flooding sum-product in the likelihood-
+ * ratio domain, double precision, <= max_iterations, early exit on zero syndrome (lib/dtl/ldpc_dec.cc:55-67).
+ * LAYERED = layered normalised min-sum, fp32, one codeword per warp (throughput mode; decodes to the
+ * same codeword whenever both converge, iteration counts differ). */
+enum { DTL_LDPC_REFERENCE = 0, DTL_LDPC_LAYERED = 1 };
+
+/* Everything the reference passes through make() arguments of the hot-path blocks
+ * (python/dtl/ofdm_receiver.py:59-246, python/dtl/ofdm_adaptive_config.py:10-89). */
+typedef struct dtl_config {
+    int32_t fft_len, cp_len;
+    int32_t frame_len;                  /* payload OFDM symbols per frame (config.py:39) */
+    int32_t header_syms;                /* 1 without FEC, 2 with (ofdm_receiver.py:66-68) */
+    /* carrier plan: flattened variable-length sets, carrier indices relative to DC (negative allowed) */
+    int32_t n_occupied_sets; const int32_t* occupied_set_len; const int32_t* occupied_carriers;
+    int32_t n_pilot_carrier_sets; const int32_t* pilot_carrier_set_len; const int32_t* pilot_carriers;
+    int32_t n_pilot_symbol_sets; const int32_t* pilot_symbol_set_len; const float* pilot_symbols; /* re,im */
+    /* ofdm_adaptive_payload_equalizer::make (include/gnuradio/dtl/ofdm_adaptive_equalizer.h:106-117) */
+    int32_t symbols_skipped; float alpha; int32_t input_is_shifted;
+    /* ofdm_adaptive_feedback_decision(hysterisis, decision_th, lut, initial) (ofdm_receiver.py:167) */
+    int32_t n_mcs; const double* mcs_snr; const int32_t* mcs_cnst; const int32_t* mcs_fec;
+    int32_t initial_mcs; double hysteresis; int32_t decision_th;
+    /* make_ldpc_decoders(alist_fnames) (lib/dtl/ldpc_dec.cc:23-31): fec id i+1 <- alist_paths[i] */
+    int32_t n_codes; const char* const* alist_paths;
+    int32_t fec_enabled;                /* FEC receive chain (soft demap + decoder) vs hard demap + frame_pack */
+    int32_t max_bps;                    /* max bits/symbol over the allowed constellations */
+    int32_t ldpc_max_iterations;        /* 15 (ldpc_dec.cc:27) */
+    int32_t ldpc_mode;                  /* DTL_LDPC_* */
+    double ldpc_sigma2;                 /* awgn_bp sigma^2; the reference never sets it -- 2.0 = "LLR in" */
+    const float* sync_word1; const float* sync_word2;   /* [fft_len] re,im shifted layout; TX only, may be NULL */
+    int32_t device;                     /* CUDA device ordinal */
+    int32_t reserved[7];
+} dtl_config;
+
+typedef struct dtl_b200 dtl_b200;
+
+/* ---- lifecycle --------------------------------------------------------------------------------------- */
+int dtl_b200_abi_version(void);
+/* Replaces the constructors of ofdm_adaptive_payload_equalizer, ofdm_adaptive_frame_equalizer_vcvc,
+ * ofdm_adaptive_constellation_soft_cf, ofdm_adaptive_fec_decoder and make_ldpc_decoders.  Fails with
+ * DTL_ERR_NO_DEVICE when no CUDA device is present. */
+dtl_status dtl_b200_create(const dtl_config* cfg, dtl_b200** out);
+void dtl_b200_destroy(dtl_b200* h);
+const char* dtl_b200_last_error(const dtl_b200* h);   /* h may be NULL: error of the last failed create */
+/* Sizes per-stream state (feedback decision, frame counters, TB reassembly carry) for n_streams and
+ * resets it -- the state a fresh flowgraph of n_streams receivers would start with. */
+dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams);
+dtl_status dtl_b200_sync(dtl_b200* h);
+void* dtl_b200_cuda_stream(dtl_b200* h);              /* cudaStream_t of the handle */
+/* derived quantities: frame_capacity (python/dtl/ofdm_adaptive.py:2-6), samples per frame incl. CP,
+ * sync and header symbols, LLR stride of one frame (floats), hard-byte stride of one frame */
+int32_t dtl_b200_frame_capacity(const dtl_b200* h);
+int32_t dtl_b200_frame_samples(const dtl_b200* h);
+int32_t dtl_b200_llr_stride(const dtl_b200* h);
+int32_t dtl_b200_bytes_stride(const dtl_b200* h);
+/* cldpc facts of code `fec_id` (1-based): n, k and (optionally) the column permutation. */
+dtl_status dtl_b200_code_info(const dtl_b200* h, int32_t fec_id, int32_t* n, int32_t* k, int32_t* permute);
+/* number of kernels this handle has launched since create (bench.py's gpu_launches) */
+uint64_t dtl_b200_launch_count(const dtl_b200* h);
+
+/* ---- stage 1: CP strip + FFT ---------------------------------------------------------------------------
+ * digital.header_payload_demux(output_symbols=True) + fft.fft_vcc(fft_len, True, (), True) on the payload
+ * symbols (python/dtl/ofdm_receiver.py:79-86,153).  iq: c64 [n_frames][frame_samples];
+ * freq: c64 [n_frames][frame_len][fft_len], DC at index fft_len/2, unnormalised. */
+dtl_status dtl_b200_demod(dtl_b200* h, const float* iq, int64_t n_frames, float* freq, int mem);
+/* fft.fft_vcc(fft_len, forward, (), shift=True) on n_vec contiguous vectors
+ * (python/dtl/ofdm_receiver.py:101,153; python/dtl/ofdm_transmitter.py:176-181). */
+dtl_status dtl_b200_fft(dtl_b200* h, const float* in, int64_t n_vec, int forward, float* out, int mem);
+
+/* ---- stages 2+3: frame equaliser (+ serialiser + demapper) ------------------------------------------------
+ * ofdm_adaptive_frame_equalizer_vcvc_impl::work (lib/dtl/ofdm_adaptive_frame_equalizer_vcvc_impl.cc:99-255)
+ * -> ofdm_adaptive_equalizer_base::frame_equalize (lib/dtl/ofdm_adaptive_equalizer.cc:217-268)
+ * -> digital.ofdm_serializer_vcc (python/dtl/ofdm_receiver.py:175-180)
+ * -> ofdm_adaptive_constellation_soft_cf_impl::general_work (lib/dtl/ofdm_adaptive_constellation_soft_cf_impl.cc:68-156)
+ *    or, without FEC, ofdm_adaptive_constellation_decoder_cb_impl::work (..._decoder_cb_impl.cc:69-93) +
+ *    ofdm_adaptive_frame_pack_bb_impl::work (lib/dtl/ofdm_adaptive_frame_pack_bb_impl.cc:73-123),
+ * fused into one pass over the frame.
+ *   freq      c64 [S*F][frame_len][fft_len]   (in)
+ *   taps      c64 [S*F][fft_len]              (in)  "ofdm_sync_chan_taps"
+ *   meta          [S*F]                        (in)
+ *   out_hard  c64 [S*F][frame_len][fft_len]   (out, optional) port 0
+ *   out_soft  c64 [S*F][frame_len][fft_len]   (out, optional) port 1 (data carriers only, as the reference)
+ *   taps_out  c64 [S*F][fft_len]              (out, optional) channel state after the frame (:186-193)
+ *   res           [S*F]                        (out, optional)
+ *   llr       f32 [S*F][llr_stride]           (out, optional) LSB-first LLRs, + = bit 1; n_llr[S*F]
+ *   bytes     u8  [S*F][bytes_stride]         (out, optional) no-FEC payload bytes (CRC stripped),
+ *   nbytes, crc_ok i32 [S*F]                   (out, optional) per frame
+ */
+dtl_status dtl_b200_equalize(dtl_b200* h, const float* freq, const float* taps, const dtl_frame_meta* meta,
+                             int32_t n_streams, int32_t frames_per_stream,
+                             float* out_hard, float* out_soft, float* taps_out, dtl_frame_result* res,
+                             float* llr, int32_t* n_llr, uint8_t* bytes, int32_t* nbytes, int32_t* crc_ok, int mem);
+
+/* ---- stage 3 stand-alone blocks -----------------------------------------------------------------------------
+ * ofdm_adaptive_constellation_soft_cf: syms c64 [n_frames][stride_syms], per frame meta.constellation,
+ * meta.packet_len symbols, noise[n_frames] = "noise_tag_key" (NULL or <0 entry: sigma = 0.001, :89);
+ * llr f32 [n_frames][stride_syms*bps_max]. */
+dtl_status dtl_b200_soft_demap(dtl_b200* h, const float* syms, int32_t stride_syms, const dtl_frame_meta* meta,
+                               const double* noise, int64_t n_frames, float* llr, int32_t llr_stride, int mem);
+/* ofdm_adaptive_constellation_decoder_cb::work: decision_maker per symbol. chunks u8 same shape as syms. */
+dtl_status dtl_b200_hard_demap(dtl_b200* h, const float* syms, int32_t stride_syms, const dtl_frame_meta* meta,
+                               int64_t n_frames, uint8_t* chunks, int mem);
+/* ofdm_adaptive_chunks_to_symbols_bc_impl::work (lib/dtl/ofdm_adaptive_chunks_to_symbols_bc_impl.cc:59-81). */
+dtl_status dtl_b200_map(dtl_b200* h, const uint8_t* chunks, int32_t stride, const dtl_frame_meta* meta,
+                        int64_t n_frames, float* syms, int mem);
+
+/* ---- stage 4: FEC decoder -----------------------------------------------------------------------------------
+ * ofdm_adaptive_fec_decoder_impl::general_work (lib/dtl/ofdm_adaptive_fec_decoder_impl.cc:80-217) +
+ * tb_decoder (lib/dtl/tb_decoder.cc:32-195) + ldpc_dec::decode (lib/dtl/ldpc_dec.cc:62-71) +
+ * ofdm_adaptive_fec_pack_bb (lib/dtl/ofdm_adaptive_fec_pack_bb_impl.cc:48-69).
+ *   llr    f32 [S*F][llr_stride] (in), meta [S*F] (in)
+ *   bytes  u8 [S][bytes_cap]: payload bytes of the CRC-passing TBs of each stream, in order; nbytes[S]
+ *   tbs       [S][tb_cap], ntbs[S]: every TB released in this call
+ */
+dtl_status dtl_b200_fec_decode(dtl_b200* h, const float* llr, int32_t llr_stride, const dtl_frame_meta* meta,
+                               int32_t n_streams, int32_t frames_per_stream,
+                               uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                               dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int mem);
+/* fec_dec::decode(const float* in, int* nit, unsigned char* out) (include/gnuradio/dtl/fec.h:25-31),
+ * `count` codewords per call: llr f32 [count][n] wire order, bits u8 [count][k], nit i32 [count]. */
+dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const float* llr, int64_t count,
+                                uint8_t* bits, int32_t* nit, int mem);
+
+/* ---- the whole receive path (stages 1-4 back to back, intermediates stay in HBM) -----------------------------
+ * in_kind 0: iq c64 [S*F][frame_samples]; 1: freq c64 [S*F][frame_len][fft_len] (stage 1 skipped).
+ * With FEC: bytes/nbytes/tbs/ntbs as dtl_b200_fec_decode.  Without: bytes [S][bytes_cap] = concatenated
+ * frame payloads, frame_crc[S*F]. */
+dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
+                       int32_t n_streams, int32_t frames_per_stream, dtl_frame_result* res,
+                       uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                       dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem);
+
+/* ---- stage 5: TX map + carrier allocation + IFFT + cyclic prefix ------------------------------------------------
+ * ofdm_adaptive_chunks_to_symbols_bc + digital.ofdm_carrier_allocator_cvc + fft.fft_vcc(N, False, (), True) +
+ * digital.ofdm_cyclic_prefixer (python/dtl/ofdm_transmitter.py:95-98,168-189).
+ *   hdr_bits u8 [n_frames][header_syms*D] (BPSK header chunks), chunks u8 [n_frames][frame_capacity],
+ *   iq c64 [n_frames][frame_samples] */
+dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const uint8_t* chunks, const dtl_frame_meta* meta,
+                       int64_t n_frames, float* iq, int mem);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTL_B200_H */
