@@ -1,0 +1,800 @@
+// api.cc -- host side of libdtl_b200.so: the C ABI of include/dtl_b200.h.
+//
+// A handle owns one CUDA stream, the device-resident tables the kernels read (carrier plan, pilot tables,
+// constellation points, twiddles, LDPC graphs), the per-stream receiver state that survives between calls
+// (feedback decision, frame counters, transport-block carry) and grow-on-demand device scratch.  Every entry
+// point only enqueues copies and kernels on that stream; DTL_MEM_HOST calls additionally wait for the outputs.
+// There is no CPU implementation behind this file: without a CUDA device dtl_b200_create fails.
+#include "kernels.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+using namespace dtl;
+
+namespace {
+
+std::mutex g_err_mu;
+std::string g_create_err;
+
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
+        size_t want = n + n / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { p = nullptr; return e; }
+        cap = want;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+enum Slot {
+    SL_IQ, SL_FREQ_IN, SL_TAPS, SL_META, SL_HARD, SL_SOFT, SL_TAPS_OUT, SL_RES, SL_LLR, SL_NLLR, SL_FBYTES, SL_FNBYTES,
+    SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
+    SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT,
+    // FEC scratch
+    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_BITS, SL_COUNT
+};
+
+} // namespace
+
+struct dtl_b200 {
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    // configuration (deep copies)
+    int N = 0, cp = 0, L = 0, H = 1, cap = 0, max_bps = 0, fec_enabled = 0;
+    int llr_stride = 0, bytes_stride = 0, frame_samples = 0;
+    int ldpc_max_it = 15, ldpc_mode = 0; double sigma2 = 2.0;
+    int n_mcs = 0, initial_mcs = 0, decision_th = 5; double hysteresis = 1.0;
+    bool have_sync = false;
+    std::vector<Code> codes;          // [n_codes + 1], entry 0 unused
+    // device tables
+    std::vector<void*> owned;
+    CnstDev cn{}; PlanDev pl{};
+    const float2* tw = nullptr; const uint32_t* crc_table = nullptr;
+    const CodeDev* d_codes = nullptr;
+    const double* d_mcs_snr = nullptr; const int* d_mcs_cnst = nullptr; const int* d_mcs_fec = nullptr;
+    const float2* d_sync1 = nullptr; const float2* d_sync2 = nullptr;
+    const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
+    int hdr_stride = 0;
+    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0;
+    // per-stream state
+    int n_streams = 0;
+    DevBuf st_buf, carry_buf, pend_buf;
+    int carry_cap = 0;
+    int* d_err = nullptr; int* d_cnt = nullptr; unsigned long long* d_bits_used = nullptr; int* d_cursor = nullptr;
+    int* h_err = nullptr;             // pinned mirror of d_err
+    DevBuf slot[SL_COUNT];
+
+    template <class T> T* upload(const std::vector<T>& v, cudaError_t& e)
+    {
+        if (e != cudaSuccess) return nullptr;
+        void* p = nullptr;
+        e = cudaMalloc(&p, std::max<size_t>(v.size() * sizeof(T), 16));
+        if (e != cudaSuccess) return nullptr;
+        owned.push_back(p);
+        if (!v.empty()) e = cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+        return (T*)p;
+    }
+};
+
+namespace {
+
+dtl_status fail(dtl_b200* h, dtl_status s, const std::string& msg)
+{
+    if (h) h->err = msg;
+    else { std::lock_guard<std::mutex> g(g_err_mu); g_create_err = msg; }
+    return s;
+}
+dtl_status cuda_fail(dtl_b200* h, cudaError_t e, const char* where)
+{
+    return fail(h, DTL_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(h, e_, #call); } while (0)
+
+int bin_of(int carrier, int N, bool shifted)
+{
+    if (carrier < 0) carrier += N;
+    return (carrier + (shifted ? N / 2 : 0)) % N;
+}
+
+// gr_expj(float(phase)) evaluated in double and rounded to float (arithmetic contract)
+float2 expj_contract(double phase)
+{
+    const float p32 = (float)phase;
+    return make_float2((float)std::cos((double)p32), (float)std::sin((double)p32));
+}
+
+int tb_ncws_host(int cw_len, int frame_len) { return frame_len > cw_len ? 1 + frame_len / cw_len : 1; }
+
+} // namespace
+
+// ---- lifecycle ---------------------------------------------------------------------------------------------------
+extern "C" int dtl_b200_abi_version(void) { return DTL_B200_ABI_VERSION; }
+
+extern "C" const char* dtl_b200_last_error(const dtl_b200* h)
+{
+    if (h) return h->err.c_str();
+    std::lock_guard<std::mutex> g(g_err_mu);
+    static thread_local std::string copy;
+    copy = g_create_err;
+    return copy.c_str();
+}
+
+extern "C" void dtl_b200_destroy(dtl_b200* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (void* p : h->owned) cudaFree(p);
+    for (auto& b : h->slot) b.release();
+    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release();
+    if (h->h_err) cudaFreeHost(h->h_err);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
+{
+    const int N = h->N, L = h->L, H = h->H;
+    const bool shifted = c->input_is_shifted != 0;
+    cudaError_t e = cudaSuccess;
+    // ---- carrier sets
+    std::vector<std::vector<int>> occ, pc; std::vector<std::vector<float2>> ps;
+    for (int s = 0, p = 0; s < c->n_occupied_sets; s++) {
+        occ.emplace_back(c->occupied_carriers + p, c->occupied_carriers + p + c->occupied_set_len[s]);
+        p += c->occupied_set_len[s];
+    }
+    for (int s = 0, p = 0; s < c->n_pilot_carrier_sets; s++) {
+        pc.emplace_back(c->pilot_carriers + p, c->pilot_carriers + p + c->pilot_carrier_set_len[s]);
+        p += c->pilot_carrier_set_len[s];
+    }
+    for (int s = 0, p = 0; s < c->n_pilot_symbol_sets; s++) {
+        std::vector<float2> v;
+        for (int k = 0; k < c->pilot_symbol_set_len[s]; k++, p++) v.push_back(make_float2(c->pilot_symbols[2 * p], c->pilot_symbols[2 * p + 1]));
+        ps.push_back(v);
+    }
+    if (pc.empty()) ps.clear();
+    for (auto& set : occ) for (int x : set) if (x < -N / 2 - N || x >= N) return fail(h, DTL_ERR_INVALID_ARG, "occupied carrier out of range");
+    const int nocc = (int)occ.size(), npc = (int)pc.size(), nps = (int)ps.size();
+    PlanDev& pl = h->pl;
+    pl.N = N; pl.L = L; pl.npc = npc; pl.nps = nps; pl.nocc = nocc;
+    pl.symbols_skipped = c->symbols_skipped;
+    pl.pcs0 = npc ? c->symbols_skipped % npc : 0;
+    pl.alpha = c->alpha; pl.oma = 1.0f - c->alpha;
+    // frame capacity (python/dtl/ofdm_adaptive.py:2-6)
+    h->cap = 0;
+    for (int i = 0; i < L; i++) h->cap += (int)occ[i % nocc].size();
+    pl.cap = h->cap;
+    // occupied mask, serialiser positions (list order), per-symbol bases for RX (ofdm_serializer_vcc, symbols_skipped = 1)
+    std::vector<uint8_t> occupied(N, 0);
+    std::vector<int16_t> ser_pos((size_t)nocc * N, -1);
+    for (int s = 0; s < nocc; s++)
+        for (size_t k = 0; k < occ[s].size(); k++) {
+            const int b = bin_of(occ[s][k], N, shifted);
+            occupied[b] = 1; ser_pos[(size_t)s * N + b] = (int16_t)k;
+        }
+    std::vector<int> ser_base(L + 1, 0);
+    for (int i = 0; i < L; i++) ser_base[i + 1] = ser_base[i] + (int)occ[(1 + i) % nocc].size();
+    // pilots of the payload equaliser (ofdm_equalizer_1d_pilots ctor + ofdm_adaptive_equalizer.cc:196-213)
+    std::vector<uint8_t> pmask((size_t)std::max(npc, 1) * N, 0);
+    std::vector<uint16_t> prank((size_t)std::max(npc, 1) * N, 0);
+    for (int s = 0; s < npc; s++) {
+        for (int x : pc[s]) pmask[(size_t)s * N + bin_of(x, N, shifted)] = 1;
+        int r = 0;
+        for (int b = 0; b < N; b++) if (pmask[(size_t)s * N + b]) prank[(size_t)s * N + b] = (uint16_t)r++;
+    }
+    std::vector<int> pprefix(L + 1, 0);
+    for (int i = 0; i < L; i++) {
+        int cnt = 0;
+        if (npc) { const int s = (pl.pcs0 + i) % npc; for (int b = 0; b < N; b++) cnt += pmask[(size_t)s * N + b]; }
+        pprefix[i + 1] = pprefix[i] + cnt;
+    }
+    pl.npil_frame = pprefix[L];
+    std::vector<float2> psym((size_t)std::max(nps, 1) * N, make_float2(0, 0)), pinv((size_t)std::max(nps, 1) * N, make_float2(0, 0));
+    for (int i = 0; i < nps; i++) {
+        const int set = i % npc;
+        for (size_t k = 0; k < pc[set].size() && k < ps[i].size(); k++) {
+            const int b = bin_of(pc[set][k], N, shifted);
+            const float2 p = ps[i][k];
+            psym[(size_t)i * N + b] = p;
+            const double re = p.x, im = p.y, d = re * re + im * im;
+            pinv[(size_t)i * N + b] = make_float2((float)(re / d), (float)(-im / d));
+        }
+    }
+    // carrier-offset phase table (frame_equalizer_vcvc_impl.cc:168-177,189-193)
+    pl.max_off = std::min(N / 2, 256);
+    std::vector<float2> ptab((size_t)(2 * pl.max_off + 1) * (L + 1));
+    for (int off = -pl.max_off; off <= pl.max_off; off++) {
+        float2* row = &ptab[(size_t)(off + pl.max_off) * (L + 1)];
+        for (int i = 0; i < L; i++) row[i] = expj_contract(-(2.0 * M_PI) * off * h->cp / N * (i + 1));
+        row[L] = expj_contract((2.0 * M_PI) * off * h->cp / N * L);
+    }
+    pl.occupied = h->upload(occupied, e); pl.pilot_mask = h->upload(pmask, e); pl.pilot_rank = h->upload(prank, e);
+    pl.pilot_prefix = h->upload(pprefix, e); pl.pilot_sym = h->upload(psym, e); pl.pilot_inv = h->upload(pinv, e);
+    pl.ser_pos = h->upload(ser_pos, e); pl.ser_base = h->upload(ser_base, e); pl.phase_tab = h->upload(ptab, e);
+
+    // ---- TX allocator tables (digital.ofdm_carrier_allocator_cvc): data symbol s = 0 is the first header symbol
+    std::vector<int> tx_base(H + L + 1, 0);
+    std::vector<uint8_t> tx_mask((size_t)(H + L) * N, 0);
+    std::vector<float2> tx_val((size_t)(H + L) * N, make_float2(0, 0));
+    for (int s = 0; s < H + L; s++) {
+        tx_base[s + 1] = tx_base[s] + (int)occ[s % nocc].size();
+        if (npc && nps) {
+            const auto& cset = pc[s % npc]; const auto& sset = ps[s % nps];
+            for (size_t k = 0; k < cset.size() && k < sset.size(); k++) {
+                const int b = bin_of(cset[k], N, true);
+                tx_mask[(size_t)s * N + b] = 1; tx_val[(size_t)s * N + b] = sset[k];
+            }
+        }
+    }
+    h->hdr_stride = tx_base[H];
+    h->d_tx_base = h->upload(tx_base, e); h->d_tx_pil_mask = h->upload(tx_mask, e); h->d_tx_pil_val = h->upload(tx_val, e);
+    if (c->sync_word1 && c->sync_word2) {
+        std::vector<float2> s1(N), s2(N);
+        for (int i = 0; i < N; i++) { s1[i] = make_float2(c->sync_word1[2 * i], c->sync_word1[2 * i + 1]); s2[i] = make_float2(c->sync_word2[2 * i], c->sync_word2[2 * i + 1]); }
+        h->d_sync1 = h->upload(s1, e); h->d_sync2 = h->upload(s2, e); h->have_sync = true;
+    }
+
+    // ---- constellations
+    std::vector<float2> pts_all, inv_all;
+    h->cn.off[0] = 0; h->cn.bps[0] = 0; h->cn.level[0] = 0; h->cn.inv2l[0] = 0;
+    for (int k = 1; k <= DTL_CNST_MAX; k++) {
+        std::vector<float2> pts, inv;
+        cnst_points(k, pts, inv, &h->cn.level[k], &h->cn.inv2l[k]);
+        h->cn.off[k] = (int)pts_all.size(); h->cn.bps[k] = cnst_bps(k);
+        pts_all.insert(pts_all.end(), pts.begin(), pts.end()); inv_all.insert(inv_all.end(), inv.begin(), inv.end());
+    }
+    h->cn.off[0] = h->cn.off[1];
+    h->cn.off[DTL_CNST_MAX + 1] = (int)pts_all.size();
+    h->cn.points = h->upload(pts_all, e); h->cn.inv_points = h->upload(inv_all, e);
+
+    // ---- twiddles exp(-2 pi i j / N), CRC-32 table (poly 0x04C11DB7 reflected, crc_util.cc:23)
+    std::vector<float2> tw(N);
+    for (int j = 0; j < N; j++) { const double a = -2.0 * M_PI * j / N; tw[j] = make_float2((float)std::cos(a), (float)std::sin(a)); }
+    h->tw = h->upload(tw, e);
+    std::vector<uint32_t> crc(256);
+    for (uint32_t i = 0; i < 256; i++) { uint32_t r = i; for (int k = 0; k < 8; k++) r = (r & 1) ? (r >> 1) ^ 0xEDB88320u : r >> 1; crc[i] = r; }
+    h->crc_table = h->upload(crc, e);
+
+    // ---- MCS look-up table (ofdm_adaptive_feedback_decision.cc:33-53: lut[0].first = DBL_MIN)
+    std::vector<double> snr(c->mcs_snr, c->mcs_snr + c->n_mcs);
+    if (!snr.empty()) snr[0] = 2.2250738585072014e-308;
+    h->d_mcs_snr = h->upload(snr, e);
+    h->d_mcs_cnst = h->upload(std::vector<int>(c->mcs_cnst, c->mcs_cnst + c->n_mcs), e);
+    h->d_mcs_fec = h->upload(std::vector<int>(c->mcs_fec, c->mcs_fec + c->n_mcs), e);
+
+    // ---- LDPC codes (make_ldpc_decoders, ldpc_dec.cc:23-59)
+    h->codes.assign(1, Code());
+    std::vector<CodeDev> cd(1);
+    memset(&cd[0], 0, sizeof(CodeDev));
+    int max_n = 0;
+    for (int i = 0; i < c->n_codes; i++) {
+        Code code; std::string err;
+        if (!load_alist(c->alist_paths[i], code, err)) return fail(h, DTL_ERR_IO, err);
+        std::vector<uint16_t> row_ptr(code.m + 1, 0), row_var, col_ptr(code.n + 1, 0), col_edge, perm(code.n);
+        for (int r = 0; r < code.m; r++) { for (int v : code.mlist[r]) row_var.push_back((uint16_t)v); row_ptr[r + 1] = (uint16_t)row_var.size(); }
+        for (int v = 0; v < code.n; v++) {
+            for (int r : code.nlist[v]) {
+                int pos = -1;
+                for (size_t q = 0; q < code.mlist[r].size(); q++) if (code.mlist[r][q] == v) pos = (int)q;
+                if (pos < 0) return fail(h, DTL_ERR_IO, "alist row/column lists disagree in " + code.path);
+                col_edge.push_back((uint16_t)(row_ptr[r] + pos));
+            }
+            col_ptr[v + 1] = (uint16_t)col_edge.size();
+        }
+        for (int q = 0; q < code.n; q++) perm[q] = (uint16_t)code.permute[q];
+        if (code.max_row > 32) return fail(h, DTL_ERR_UNSUPPORTED, "LDPC row weight > 32");
+        CodeDev& d = code.dev;
+        d.n = code.n; d.m = code.m; d.k = code.k; d.rank = code.rank; d.edges = code.edges; d.max_row = code.max_row; d.max_col = code.max_col;
+        d.row_ptr = h->upload(row_ptr, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
+        d.col_edge = h->upload(col_edge, e); d.permute = h->upload(perm, e);
+        cd.push_back(d);
+        max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
+        h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, code.edges));
+        h->codes.push_back(std::move(code));
+    }
+    h->d_codes = h->upload(cd, e);
+    if (max_n) {
+        h->max_ncws = tb_ncws_host(max_n, h->cap * h->max_bps);       // fec_decoder_impl.cc:54-72
+        h->max_tb = max_n * h->max_ncws;
+        // codes with a smaller n split a frame into more codewords
+        for (size_t i = 1; i < h->codes.size(); i++) h->max_ncws = std::max(h->max_ncws, tb_ncws_host(h->codes[i].n, 8 * ((h->cap * h->max_bps + 7) / 8)));
+        h->carry_cap = 2 * h->max_tb;
+    }
+    if (e != cudaSuccess) return cuda_fail(h, e, "table upload");
+    return DTL_OK;
+}
+
+extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
+{
+    if (!out) return DTL_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (!c) return fail(nullptr, DTL_ERR_INVALID_ARG, "null config");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0)
+        return fail(nullptr, DTL_ERR_NO_DEVICE, std::string("no CUDA device (") + cudaGetErrorString(e) + "); libdtl_b200 has no CPU path");
+    if (c->device < 0 || c->device >= ndev) return fail(nullptr, DTL_ERR_INVALID_ARG, "device ordinal out of range");
+    const int N = c->fft_len;
+    if (N < 8 || N > 1024 || (N & (N - 1))) return fail(nullptr, DTL_ERR_UNSUPPORTED, "fft_len must be a power of two in [8, 1024]");
+    if (c->cp_len < 0 || c->cp_len > N) return fail(nullptr, DTL_ERR_INVALID_ARG, "cp_len out of range");
+    if (c->frame_len < 1 || c->frame_len > (N > 256 ? 20 : 40)) return fail(nullptr, DTL_ERR_UNSUPPORTED, "frame_len out of range");
+    if (c->n_occupied_sets < 1 || !c->occupied_set_len || !c->occupied_carriers) return fail(nullptr, DTL_ERR_INVALID_ARG, "occupied carriers missing");
+    if (c->n_mcs < 1 || !c->mcs_snr || !c->mcs_cnst || !c->mcs_fec || c->initial_mcs < 0 || c->initial_mcs >= c->n_mcs)
+        return fail(nullptr, DTL_ERR_INVALID_ARG, "MCS look-up table missing (\"Feedback lookup table is empty\")");
+    if (c->max_bps < 1 || c->max_bps > 8) return fail(nullptr, DTL_ERR_INVALID_ARG, "max_bps out of range");
+    if (c->fec_enabled && c->n_codes < 1) return fail(nullptr, DTL_ERR_INVALID_ARG, "Misconfiguration: decoder not found!");
+    dtl_b200* h = new dtl_b200;
+    h->device = c->device;
+    auto bail = [&](dtl_status s) { { std::lock_guard<std::mutex> g(g_err_mu); g_create_err = h->err; } dtl_b200_destroy(h); return s; };
+    if ((e = cudaSetDevice(h->device)) != cudaSuccess) { cuda_fail(h, e, "cudaSetDevice"); return bail(DTL_ERR_CUDA); }
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, h->device)) != cudaSuccess) { cuda_fail(h, e, "cudaGetDeviceProperties"); return bail(DTL_ERR_CUDA); }
+    if (prop.major != 10) { fail(h, DTL_ERR_UNSUPPORTED, "libdtl_b200 is built for sm_100a only"); return bail(DTL_ERR_UNSUPPORTED); }
+    h->sm_count = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { cuda_fail(h, e, "cudaStreamCreate"); return bail(DTL_ERR_CUDA); }
+    h->N = N; h->cp = c->cp_len; h->L = c->frame_len; h->H = c->header_syms > 0 ? c->header_syms : (c->fec_enabled ? 2 : 1);
+    h->max_bps = c->max_bps; h->fec_enabled = c->fec_enabled;
+    h->ldpc_max_it = c->ldpc_max_iterations > 0 ? c->ldpc_max_iterations : 15;
+    h->ldpc_mode = c->ldpc_mode; h->sigma2 = c->ldpc_sigma2 > 0 ? c->ldpc_sigma2 : 2.0;
+    h->n_mcs = c->n_mcs; h->initial_mcs = c->initial_mcs; h->decision_th = c->decision_th; h->hysteresis = c->hysteresis;
+    dtl_status s = build_tables(h, c);
+    if (s != DTL_OK) return bail(s);
+    h->llr_stride = h->cap * h->max_bps;
+    h->bytes_stride = (((h->cap * h->max_bps + 7) / 8) + 3) & ~3;
+    h->frame_samples = (h->L + h->H + 2) * (h->N + h->cp);
+    void* p = nullptr;
+    if ((e = cudaMalloc(&p, 64)) != cudaSuccess) { cuda_fail(h, e, "cudaMalloc"); return bail(DTL_ERR_CUDA); }
+    h->owned.push_back(p);
+    cudaMemset(p, 0, 64);
+    h->d_err = (int*)p; h->d_cnt = (int*)p + 4; h->d_cursor = (int*)p + 8; h->d_bits_used = (unsigned long long*)((char*)p + 48);
+    if ((e = cudaHostAlloc((void**)&h->h_err, 64, cudaHostAllocDefault)) != cudaSuccess) { cuda_fail(h, e, "cudaHostAlloc"); return bail(DTL_ERR_CUDA); }
+    *h->h_err = 0;
+    *out = h;
+    return DTL_OK;
+}
+
+// ---- state, sync, getters ---------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams)
+{
+    if (!h || n_streams < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<StreamState> st((size_t)n_streams);
+    for (auto& s : st) {
+        memset(&s, 0, sizeof(s));
+        s.fb_last = s.fb_next = h->initial_mcs;      // ofdm_adaptive_feedback_decision.cc:33-53
+        s.tb_number = -1;                             // tb_decoder.cc:21-30
+    }
+    CK(h->st_buf.ensure(std::max<size_t>(st.size() * sizeof(StreamState), 16)));
+    if (n_streams) CK(cudaMemcpy(h->st_buf.p, st.data(), st.size() * sizeof(StreamState), cudaMemcpyHostToDevice));
+    if (h->carry_cap) CK(h->carry_buf.ensure((size_t)n_streams * h->carry_cap * sizeof(float) + 16));
+    CK(h->pend_buf.ensure((size_t)n_streams * sizeof(TbDesc) + 16));
+    CK(cudaMemset(h->d_err, 0, sizeof(int)));
+    h->n_streams = n_streams;
+    return DTL_OK;
+}
+
+static dtl_status check_device_error(dtl_b200* h)
+{
+    const int e = *h->h_err;
+    if (!e) return DTL_OK;
+    *h->h_err = 0;
+    cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream);
+    char buf[160];
+    snprintf(buf, sizeof buf, "device error word 0x%x", e);
+    if (e & 1) return fail(h, DTL_ERR_MISSING_TAG, std::string(buf) + ": Missing constellation tag / unknown constellation");
+    if (e & (4 | 8)) return fail(h, DTL_ERR_MISSING_TAG, std::string(buf) + ": Tags missing / FEC tags missing");
+    if (e & 2) return fail(h, DTL_ERR_UNSUPPORTED, std::string(buf) + ": carrier offset beyond the phase table");
+    if (e & (16 | 32 | 64 | 512)) return fail(h, DTL_ERR_CAPACITY, std::string(buf) + ": output buffer or transport-block table too small");
+    return fail(h, DTL_ERR_INVALID_ARG, std::string(buf) + ": inconsistent transport-block tags");
+}
+
+extern "C" dtl_status dtl_b200_sync(dtl_b200* h)
+{
+    if (!h) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return check_device_error(h);
+}
+
+extern "C" void* dtl_b200_cuda_stream(dtl_b200* h) { return h ? (void*)h->stream : nullptr; }
+extern "C" int32_t dtl_b200_frame_capacity(const dtl_b200* h) { return h ? h->cap : 0; }
+extern "C" int32_t dtl_b200_frame_samples(const dtl_b200* h) { return h ? h->frame_samples : 0; }
+extern "C" int32_t dtl_b200_llr_stride(const dtl_b200* h) { return h ? h->llr_stride : 0; }
+extern "C" int32_t dtl_b200_bytes_stride(const dtl_b200* h) { return h ? h->bytes_stride : 0; }
+extern "C" uint64_t dtl_b200_launch_count(const dtl_b200* h) { return h ? h->launches : 0; }
+
+extern "C" dtl_status dtl_b200_code_info(const dtl_b200* h, int32_t fec_id, int32_t* n, int32_t* k, int32_t* permute)
+{
+    if (!h || fec_id < 1 || fec_id >= (int)h->codes.size()) return DTL_ERR_INVALID_ARG;
+    const Code& c = h->codes[fec_id];
+    if (n) *n = c.n;
+    if (k) *k = c.k;
+    if (permute) for (int i = 0; i < c.n; i++) permute[i] = c.permute[i];
+    return DTL_OK;
+}
+
+extern "C" dtl_status dtl_b200_host_alloc(void** out, size_t bytes)
+{
+    if (!out) return DTL_ERR_INVALID_ARG;
+    return cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? DTL_OK : DTL_ERR_CUDA;
+}
+extern "C" void dtl_b200_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---- staging: user pointer -> device pointer ----------------------------------------------------------------------------------
+namespace {
+
+struct Stage {
+    dtl_b200* h; int mem; cudaError_t e = cudaSuccess;
+    struct Out { void* user; void* dev; size_t bytes; };
+    std::vector<Out> outs;
+    Stage(dtl_b200* h_, int mem_) : h(h_), mem(mem_) {}
+    template <class T> const T* in(int slot, const T* user, size_t count)
+    {
+        if (!user || mem == DTL_MEM_DEVICE || e != cudaSuccess) return user;
+        DevBuf& b = h->slot[slot];
+        if ((e = b.ensure(count * sizeof(T) + 16)) != cudaSuccess) return nullptr;
+        e = cudaMemcpyAsync(b.p, user, count * sizeof(T), cudaMemcpyHostToDevice, h->stream);
+        return (const T*)b.p;
+    }
+    template <class T> T* out(int slot, T* user, size_t count)
+    {
+        if (!user || mem == DTL_MEM_DEVICE || e != cudaSuccess) return user;
+        DevBuf& b = h->slot[slot];
+        if ((e = b.ensure(count * sizeof(T) + 16)) != cudaSuccess) return nullptr;
+        outs.push_back({ (void*)user, b.p, count * sizeof(T) });
+        return (T*)b.p;
+    }
+    // device scratch that is needed whether or not the caller wants the data back
+    template <class T> T* scratch(int slot, size_t count)
+    {
+        if (e != cudaSuccess) return nullptr;
+        DevBuf& b = h->slot[slot];
+        if ((e = b.ensure(count * sizeof(T) + 16)) != cudaSuccess) return nullptr;
+        return (T*)b.p;
+    }
+    dtl_status finish()
+    {
+        if (e != cudaSuccess) return cuda_fail(h, e, "staging");
+        if (mem == DTL_MEM_DEVICE) return DTL_OK;
+        for (auto& o : outs)
+            if ((e = cudaMemcpyAsync(o.user, o.dev, o.bytes, cudaMemcpyDeviceToHost, h->stream)) != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync D2H");
+        return dtl_b200_sync(h);
+    }
+};
+
+dtl_status ensure_streams(dtl_b200* h, int n_streams)
+{
+    if (h->n_streams == n_streams) return DTL_OK;
+    return dtl_b200_reset(h, n_streams);
+}
+
+// host-side tag validation for DTL_MEM_HOST calls (the device re-checks and reports through the error word)
+dtl_status check_meta_host(dtl_b200* h, const dtl_frame_meta* meta, long long n, int mem)
+{
+    if (mem != DTL_MEM_HOST || !meta) return DTL_OK;
+    for (long long f = 0; f < n; f++) {
+        if (meta[f].constellation == DTL_CNST_UNKNOWN) return fail(h, DTL_ERR_MISSING_TAG, "Missing constellation tag.");
+        if (meta[f].constellation < 0 || meta[f].constellation > DTL_CNST_MAX) return fail(h, DTL_ERR_INVALID_ARG, "Unknown constellation");
+    }
+    return DTL_OK;
+}
+
+} // namespace
+
+// ---- device-level stages (all pointers are device pointers) ---------------------------------------------------------------------
+namespace {
+
+dtl_status dev_demod(dtl_b200* h, const float2* iq, long long n_frames, float2* freq)
+{
+    CK(launch_fft_fwd(h->stream, iq, freq, n_frames * h->L, h->L, h->frame_samples, h->H + 2, h->N + h->cp, h->cp, h->N, h->tw));
+    h->launches += 1;
+    return DTL_OK;
+}
+
+dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2* taps, const dtl_frame_meta* meta, int S, int F,
+                        float2* out_hard, float2* out_soft, float2* taps_out, dtl_frame_result* res,
+                        float* llr, int* n_llr, uint8_t* fbytes, int* fnbytes, int* fcrc)
+{
+    const long long n = (long long)S * F;
+    if (!res) res = sg.scratch<dtl_frame_result>(SL_RES, (size_t)n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
+    EqParams p;
+    memset(&p, 0, sizeof p);
+    p.pl = h->pl; p.cn = h->cn; p.freq = freq; p.taps = taps; p.meta = meta; p.n_frames = n;
+    p.out_hard = out_hard; p.out_soft = out_soft; p.taps_out = taps_out; p.res = res;
+    p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr;
+    p.bytes = fbytes; p.bytes_stride = h->bytes_stride; p.nbytes = fnbytes; p.crc_ok = fcrc;
+    p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
+    CK(launch_eq(h->stream, p));
+    StreamParams sp;
+    sp.st = (StreamState*)h->st_buf.p; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
+    sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
+    sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
+    CK(launch_stream_state(h->stream, sp));
+    h->launches += 2;
+    return DTL_OK;
+}
+
+dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, const dtl_frame_meta* meta, int S, int F,
+                   uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs)
+{
+    if (h->codes.size() < 2) return fail(h, DTL_ERR_INVALID_ARG, "Misconfiguration: decoder not found!");
+    FecParams p;
+    memset(&p, 0, sizeof p);
+    const size_t tb_slots = 2 * (size_t)F + 1, budget = (size_t)S * ((size_t)F + 2);
+    p.st = (StreamState*)h->st_buf.p; p.n_streams = S; p.F = F; p.meta = meta; p.llr = llr; p.llr_stride = llr_stride;
+    p.carry = (float*)h->carry_buf.p; p.carry_cap = h->carry_cap;
+    p.n_codes = (int)h->codes.size() - 1; p.codes = h->d_codes; p.cap = h->cap;
+    for (int c = 0; c <= DTL_CNST_MAX; c++) p.bps_tab[c] = cnst_bps(c);
+    p.max_tb = h->max_tb;
+    p.tb_slots = (int)tb_slots;
+    p.tbs = sg.scratch<TbDesc>(SL_TBDESC, (size_t)S * tb_slots);
+    p.pend = (TbDesc*)h->pend_buf.p;
+    p.tres = sg.scratch<dtl_tb_result>(SL_TRES, (size_t)S * tb_slots);
+    p.tb_count = sg.scratch<int>(SL_TBCOUNT, (size_t)S);
+    p.tb_list = sg.scratch<int>(SL_TBLIST, (size_t)S * tb_slots);
+    p.cw_cap = (int)std::min<size_t>(budget * h->max_ncws, 0x7fffffff);
+    p.cw_tb = sg.scratch<int>(SL_CWTB, (size_t)p.cw_cap);
+    p.cw_nit = sg.scratch<int>(SL_CWNIT, (size_t)p.cw_cap);
+    p.bits_cap = (long long)budget * ((long long)h->max_ncws * h->max_k + 4);
+    p.bits = sg.scratch<uint8_t>(SL_BITS, (size_t)p.bits_cap + 64);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");
+    p.cnt = h->d_cnt; p.bits_used = h->d_bits_used;
+    p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode; p.warp_bytes = h->warp_bytes;
+    p.bytes = bytes; p.bytes_cap = bytes_cap; p.nbytes = nbytes; p.tb_out = tbs; p.tb_cap = tb_cap; p.ntbs = ntbs;
+    p.crc_table = h->crc_table; p.err = h->d_err;
+    int launches = 0;
+    CK(launch_fec(h->stream, p, h->sm_count, &launches));
+    h->launches += launches;
+    return DTL_OK;
+}
+
+} // namespace
+
+// ---- stage 1 -----------------------------------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_demod(dtl_b200* h, const float* iq, int64_t n_frames, float* freq, int mem)
+{
+    if (!h || !iq || !freq || n_frames < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    Stage sg(h, mem);
+    const float2* d_iq = sg.in(SL_IQ, (const float2*)iq, (size_t)n_frames * h->frame_samples);
+    float2* d_freq = sg.out(SL_FREQ, (float2*)freq, (size_t)n_frames * h->L * h->N);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    dtl_status s = dev_demod(h, d_iq, n_frames, d_freq);
+    if (s != DTL_OK) return s;
+    return sg.finish();
+}
+
+extern "C" dtl_status dtl_b200_fft(dtl_b200* h, const float* in, int64_t n_vec, int forward, float* out, int mem)
+{
+    if (!h || !in || !out || n_vec < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    Stage sg(h, mem);
+    const float2* d_in = sg.in(SL_FFT_IN, (const float2*)in, (size_t)n_vec * h->N);
+    float2* d_out = sg.out(SL_FFT_OUT, (float2*)out, (size_t)n_vec * h->N);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    if (forward) CK(launch_fft_fwd(h->stream, d_in, d_out, n_vec, 1, h->N, 0, h->N, 0, h->N, h->tw));
+    else CK(launch_fft_inv(h->stream, d_in, d_out, n_vec, h->N, h->tw));
+    h->launches += 1;
+    return sg.finish();
+}
+
+// ---- stages 2+3 ----------------------------------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_equalize(dtl_b200* h, const float* freq, const float* taps, const dtl_frame_meta* meta,
+                                        int32_t n_streams, int32_t frames_per_stream,
+                                        float* out_hard, float* out_soft, float* taps_out, dtl_frame_result* res,
+                                        float* llr, int32_t* n_llr, uint8_t* bytes, int32_t* nbytes, int32_t* crc_ok, int mem)
+{
+    if (!h || !freq || !taps || !meta || n_streams < 0 || frames_per_stream < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t n = (size_t)n_streams * frames_per_stream, LN = (size_t)h->L * h->N;
+    dtl_status s = check_meta_host(h, meta, (long long)n, mem);
+    if (s != DTL_OK) return s;
+    if ((s = ensure_streams(h, n_streams)) != DTL_OK) return s;
+    Stage sg(h, mem);
+    const float2* d_freq = sg.in(SL_FREQ_IN, (const float2*)freq, n * LN);
+    const float2* d_taps = sg.in(SL_TAPS, (const float2*)taps, n * h->N);
+    const dtl_frame_meta* d_meta = sg.in(SL_META, meta, n);
+    float2* d_hard = sg.out(SL_HARD, (float2*)out_hard, n * LN);
+    float2* d_soft = sg.out(SL_SOFT, (float2*)out_soft, n * LN);
+    float2* d_tout = sg.out(SL_TAPS_OUT, (float2*)taps_out, n * h->N);
+    dtl_frame_result* d_res = sg.out(SL_RES, res, n);
+    float* d_llr = sg.out(SL_LLR, llr, n * h->llr_stride);
+    int* d_nllr = sg.out(SL_NLLR, n_llr, n);
+    uint8_t* d_bytes = sg.out(SL_FBYTES, bytes, n * h->bytes_stride);
+    int* d_nb = sg.out(SL_FNBYTES, nbytes, n);
+    int* d_crc = sg.out(SL_FCRC, crc_ok, n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    if (mem == DTL_MEM_HOST && d_soft) CK(cudaMemsetAsync(d_soft, 0, n * LN * sizeof(float2), h->stream));
+    if ((nbytes || crc_ok) && !bytes) d_bytes = sg.scratch<uint8_t>(SL_FBYTES, n * h->bytes_stride);
+    s = dev_equalize(h, sg, d_freq, d_taps, d_meta, n_streams, frames_per_stream, d_hard, d_soft, d_tout, d_res, d_llr, d_nllr,
+                     d_bytes, d_nb, d_crc);
+    if (s != DTL_OK) return s;
+    return sg.finish();
+}
+
+// ---- stage 3 / 5a stand-alone blocks -------------------------------------------------------------------------------------------------
+static dtl_status demap_common(dtl_b200* h, int mode, const float* syms, const uint8_t* in_chunks, int32_t stride_syms,
+                               const dtl_frame_meta* meta, const double* noise, int64_t n_frames, float* llr, int32_t llr_stride,
+                               uint8_t* chunks, float* out_syms, int mem)
+{
+    if (!h || !meta || n_frames < 0 || stride_syms <= 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    dtl_status s = check_meta_host(h, meta, n_frames, mem);
+    if (s != DTL_OK) return s;
+    const size_t n = (size_t)n_frames;
+    Stage sg(h, mem);
+    DemapParams p;
+    memset(&p, 0, sizeof p);
+    p.cn = h->cn; p.stride_syms = stride_syms; p.n_frames = n_frames; p.llr_stride = llr_stride; p.mode = mode;
+    p.meta = sg.in(SL_META, meta, n);
+    p.syms = sg.in(SL_SYMS, (const float2*)syms, n * stride_syms);
+    p.in_chunks = sg.in(SL_CHUNKS, in_chunks, n * stride_syms);
+    p.noise = sg.in(SL_NOISE, noise, n);
+    p.llr = sg.out(SL_LLR, llr, n * (size_t)llr_stride);
+    p.chunks = sg.out(SL_BITS_OUT, chunks, n * stride_syms);
+    p.out_syms = sg.out(SL_SOFT, (float2*)out_syms, n * stride_syms);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    CK(launch_demap(h->stream, p));
+    h->launches += 1;
+    return sg.finish();
+}
+
+extern "C" dtl_status dtl_b200_soft_demap(dtl_b200* h, const float* syms, int32_t stride_syms, const dtl_frame_meta* meta,
+                                          const double* noise, int64_t n_frames, float* llr, int32_t llr_stride, int mem)
+{
+    if (!syms || !llr || llr_stride < stride_syms) return DTL_ERR_INVALID_ARG;
+    return demap_common(h, 0, syms, nullptr, stride_syms, meta, noise, n_frames, llr, llr_stride, nullptr, nullptr, mem);
+}
+extern "C" dtl_status dtl_b200_hard_demap(dtl_b200* h, const float* syms, int32_t stride_syms, const dtl_frame_meta* meta,
+                                          int64_t n_frames, uint8_t* chunks, int mem)
+{
+    if (!syms || !chunks) return DTL_ERR_INVALID_ARG;
+    return demap_common(h, 1, syms, nullptr, stride_syms, meta, nullptr, n_frames, nullptr, 0, chunks, nullptr, mem);
+}
+extern "C" dtl_status dtl_b200_map(dtl_b200* h, const uint8_t* chunks, int32_t stride, const dtl_frame_meta* meta,
+                                   int64_t n_frames, float* syms, int mem)
+{
+    if (!chunks || !syms) return DTL_ERR_INVALID_ARG;
+    return demap_common(h, 2, nullptr, chunks, stride, meta, nullptr, n_frames, nullptr, 0, nullptr, syms, mem);
+}
+
+// ---- stage 4 ---------------------------------------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_fec_decode(dtl_b200* h, const float* llr, int32_t llr_stride, const dtl_frame_meta* meta,
+                                          int32_t n_streams, int32_t frames_per_stream,
+                                          uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                                          dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int mem)
+{
+    if (!h || !llr || !meta || n_streams < 0 || frames_per_stream < 0 || llr_stride <= 0) return DTL_ERR_INVALID_ARG;
+    if ((bytes && bytes_cap <= 0) || (tbs && tb_cap <= 0)) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    const size_t n = (size_t)n_streams * frames_per_stream;
+    dtl_status s = ensure_streams(h, n_streams);
+    if (s != DTL_OK) return s;
+    Stage sg(h, mem);
+    const float* d_llr = sg.in(SL_LLR, llr, n * (size_t)llr_stride);
+    const dtl_frame_meta* d_meta = sg.in(SL_META, meta, n);
+    uint8_t* d_bytes = sg.out(SL_BYTES, bytes, (size_t)n_streams * bytes_cap);
+    int* d_nb = sg.out(SL_NBYTES, nbytes, (size_t)n_streams);
+    dtl_tb_result* d_tbs = sg.out(SL_TBS_OUT, tbs, (size_t)n_streams * tb_cap);
+    int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)n_streams);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    s = dev_fec(h, sg, d_llr, llr_stride, d_meta, n_streams, frames_per_stream, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt);
+    if (s != DTL_OK) return s;
+    return sg.finish();
+}
+
+extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const float* llr, int64_t count,
+                                           uint8_t* bits, int32_t* nit, int mem)
+{
+    if (!h || !llr || !bits || count < 0) return DTL_ERR_INVALID_ARG;
+    if (fec_id < 1 || fec_id >= (int)h->codes.size()) return fail(h, DTL_ERR_MISSING_TAG, "FEC tags missing");
+    CK(cudaSetDevice(h->device));
+    const Code& c = h->codes[fec_id];
+    Stage sg(h, mem);
+    LdpcParams p;
+    memset(&p, 0, sizeof p);
+    p.code = c.dev; p.count = count; p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode;
+    p.cursor = h->d_cursor; p.warp_bytes = h->warp_bytes;
+    p.llr = sg.in(SL_LLR, llr, (size_t)count * c.n);
+    p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
+    p.nit = sg.out(SL_NIT, nit, (size_t)count);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    CK(launch_ldpc(h->stream, p, h->sm_count));
+    h->launches += 2;
+    return sg.finish();
+}
+
+// ---- the whole receive path ---------------------------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
+                                  int32_t n_streams, int32_t frames_per_stream, dtl_frame_result* res,
+                                  uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                                  dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem)
+{
+    if (!h || !in || !taps || !meta || n_streams < 0 || frames_per_stream < 0 || (in_kind != 0 && in_kind != 1)) return DTL_ERR_INVALID_ARG;
+    if ((bytes && bytes_cap <= 0) || (tbs && tb_cap <= 0)) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    const int S = n_streams, F = frames_per_stream;
+    const size_t n = (size_t)S * F, LN = (size_t)h->L * h->N;
+    dtl_status s = check_meta_host(h, meta, (long long)n, mem);
+    if (s != DTL_OK) return s;
+    if ((s = ensure_streams(h, S)) != DTL_OK) return s;
+    Stage sg(h, mem);
+    const float2* d_in = in_kind == 0 ? sg.in(SL_IQ, (const float2*)in, n * h->frame_samples) : sg.in(SL_FREQ_IN, (const float2*)in, n * LN);
+    const float2* d_taps = sg.in(SL_TAPS, (const float2*)taps, n * h->N);
+    const dtl_frame_meta* d_meta = sg.in(SL_META, meta, n);
+    dtl_frame_result* d_res = sg.out(SL_RES, res, n);
+    uint8_t* d_bytes = sg.out(SL_BYTES, bytes, (size_t)S * bytes_cap);
+    int* d_nb = sg.out(SL_NBYTES, nbytes, (size_t)S);
+    dtl_tb_result* d_tbs = sg.out(SL_TBS_OUT, tbs, (size_t)S * tb_cap);
+    int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
+    int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
+    const float2* d_freq = d_in;
+    if (in_kind == 0) {
+        float2* fq = sg.scratch<float2>(SL_FREQ, n * LN);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        if ((s = dev_demod(h, d_in, (long long)n, fq)) != DTL_OK) return s;
+        d_freq = fq;
+    }
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    if (h->fec_enabled) {
+        float* d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
+        if (s != DTL_OK) return s;
+        s = dev_fec(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt);
+        if (s != DTL_OK) return s;
+    } else {
+        uint8_t* fb = sg.scratch<uint8_t>(SL_FBYTES, n * h->bytes_stride);
+        int* fnb = sg.scratch<int>(SL_FNBYTES, n);
+        if (!d_fcrc) d_fcrc = sg.scratch<int>(SL_FCRC, n);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, nullptr, nullptr, fb, fnb, d_fcrc);
+        if (s != DTL_OK) return s;
+        if (d_bytes || d_nb) {
+            CK(launch_frame_gather(h->stream, fb, h->bytes_stride, fnb, S, F, d_bytes, d_bytes ? bytes_cap : 0, d_nb, h->d_err));
+            h->launches += 1;
+        }
+        if (d_nt) CK(cudaMemsetAsync(d_nt, 0, (size_t)S * sizeof(int), h->stream));
+    }
+    return sg.finish();
+}
+
+// ---- stage 5 --------------------------------------------------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const uint8_t* chunks, const dtl_frame_meta* meta,
+                                  int64_t n_frames, float* iq, int mem)
+{
+    if (!h || !hdr_bits || !chunks || !meta || !iq || n_frames < 0) return DTL_ERR_INVALID_ARG;
+    if (!h->have_sync) return fail(h, DTL_ERR_INVALID_ARG, "sync words were not configured");
+    CK(cudaSetDevice(h->device));
+    dtl_status s = check_meta_host(h, meta, n_frames, mem);
+    if (s != DTL_OK) return s;
+    const size_t n = (size_t)n_frames;
+    Stage sg(h, mem);
+    TxParams p;
+    memset(&p, 0, sizeof p);
+    p.N = h->N; p.cp = h->cp; p.H = h->H; p.L = h->L; p.cap = h->cap; p.nocc = h->pl.nocc; p.hdr_stride = h->hdr_stride;
+    p.n_frames = n_frames;
+    p.hdr_bits = sg.in(SL_HDR, hdr_bits, n * h->hdr_stride);
+    p.chunks = sg.in(SL_CHUNKS, chunks, n * h->cap);
+    p.meta = sg.in(SL_META, meta, n);
+    p.iq = sg.out(SL_TXIQ, (float2*)iq, n * h->frame_samples);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    p.sync1 = h->d_sync1; p.sync2 = h->d_sync2; p.ser_pos = h->pl.ser_pos; p.tx_base = h->d_tx_base;
+    p.tx_pil_mask = h->d_tx_pil_mask; p.tx_pil_val = h->d_tx_pil_val; p.tw = h->tw; p.cn = h->cn;
+    CK(launch_tx_mod(h->stream, p));
+    h->launches += 1;
+    return sg.finish();
+}

@@ -86,5 +86,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
 size_t ldpc_warp_bytes(int n, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
 cudaError_t launch_demap(cudaStream_t st, const DemapParams& p);   // mode 0 soft, 1 hard, 2 map
+cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int bytes_stride, const int* fn, int n_streams, int F,
+                                uint8_t* out, int cap, int* out_n, int* err);
 
 } // namespace dtl

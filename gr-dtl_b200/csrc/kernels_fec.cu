@@ -330,3 +330,149 @@ __global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
     }
 }
 
+
+// ---- TB epilogue: bits -> bytes LSB-first, CRC-32 verify (fec_decoder_impl.cc:161-204) -------------------------
+// One warp per released TB.  The TB's bits (one per byte) are packed in place: the 32 bits of word w are
+// read by the 32 lanes before lane 0 overwrites bytes [4w, 4w+4), which only cover bits already consumed.
+__global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
+{
+    __shared__ uint32_t crc_tab[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) crc_tab[i] = p.crc_table[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= p.cnt[2]) return;
+    const int gi = p.tb_list[t];
+    const TbDesc& d = p.tbs[gi];
+    uint8_t* bits = p.bits + d.bit_base;
+    const int user = d.payload_len - 32;
+    int nit_sum = 0;
+    for (int i = lane; i < d.ncws; i += 32) nit_sum += p.cw_nit[d.cw_first + i];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) nit_sum += __shfl_xor_sync(0xffffffffu, nit_sum, o);
+    dtl_tb_result r;
+    r.tb_no = d.tb_no; r.crc_ok = 0; r.nbytes = 0; r.avg_it = nit_sum / d.ncws; r.frame_index = d.frame_index;
+    if (user >= 0) {
+        const uint32_t stored = __ballot_sync(0xffffffffu, bits[user + lane] & 1);   // little-endian CRC field
+        __syncwarp();
+        const int words = (user + 31) >> 5;
+        for (int w = 0; w < words; w++) {
+            const int b = w * 32 + lane;
+            const uint32_t word = __ballot_sync(0xffffffffu, b < user && (bits[b] & 1));
+            __syncwarp();
+            if (lane == 0) ((uint32_t*)bits)[w] = word;
+            __syncwarp();
+        }
+        const int n0 = (user + 7) >> 3;
+        uint32_t crc = 0xFFFFFFFFu;
+        if (lane == 0) {
+            for (int b = 0; b < n0; b++) crc = crc_tab[(crc ^ bits[b]) & 0xffu] ^ (crc >> 8);
+            crc = ~crc;
+        }
+        crc = __shfl_sync(0xffffffffu, crc, 0);
+        r.crc_ok = crc == stored;
+        r.nbytes = r.crc_ok ? user >> 3 : 0;
+    }
+    if (lane == 0) p.tres[gi] = r;
+}
+
+// One warp per stream: concatenate the payload bytes of its CRC-passing TBs in release order
+// (ofdm_adaptive_fec_pack_bb) and compact the per-TB monitor records.
+__global__ void __launch_bounds__(256) tb_gather_kernel(FecParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (s >= p.n_streams) return;
+    const int ntb = p.tb_count[s];
+    int pos = 0, err = 0;
+    for (int i = 0; i < ntb; i++) {
+        const int gi = s * p.tb_slots + i;
+        const dtl_tb_result r = p.tres[gi];
+        if (p.tb_out && i < p.tb_cap && lane == 0) p.tb_out[(size_t)s * p.tb_cap + i] = r;
+        if (r.nbytes > 0 && p.bytes) {
+            if (pos + r.nbytes <= p.bytes_cap) {
+                const uint8_t* src = p.bits + p.tbs[gi].bit_base;
+                uint8_t* dst = p.bytes + (size_t)s * p.bytes_cap + pos;
+                for (int b = lane; b < r.nbytes; b += 32) dst[b] = src[b];
+            } else err = ERR_BITS_CAP;
+        }
+        pos += r.nbytes;
+    }
+    if (p.tb_out && ntb > p.tb_cap) err |= ERR_TB_SLOTS;
+    if (lane == 0) {
+        if (p.nbytes) p.nbytes[s] = pos;
+        if (p.ntbs) p.ntbs[s] = ntb;
+        if (err) atomicOr(p.err, err);
+    }
+}
+
+// One warp per stream: LLRs of the TB still in flight move behind what the carry buffer already holds.
+__global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (s >= p.n_streams) return;
+    const TbDesc& d = p.pend[s];
+    float* carry = p.carry + (size_t)s * p.carry_cap;
+    int base = 0;
+    for (int i = 0; i < d.nseg; i++) {
+        const TbSeg sg = d.seg[i];
+        if (sg.src >= 0) {
+            const float* src = p.llr + ((size_t)s * p.F + sg.src) * p.llr_stride + sg.start;
+            for (int q = lane; q < sg.len; q += 32) carry[base + q] = src[q];
+        }                                      // src < 0: the carry segment is always first and already in place
+        base += sg.len;
+    }
+}
+
+__global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = 0; *bits_used = 0ull; }
+
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches)
+{
+    if (p.n_streams <= 0 || p.F <= 0) return cudaSuccess;
+    fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
+    tb_plan_kernel<<<(p.n_streams + 127) / 128, 128, 0, st>>>(p);
+    const int warps = 8;
+    const size_t smem = (size_t)p.warp_bytes * warps;
+    if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+    static size_t attr_set = 0;
+    if (smem > 48 * 1024 && smem > attr_set) {
+        cudaFuncSetAttribute(ldpc_tb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = smem;
+    }
+    int per_sm = (int)((220 * 1024) / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 8) per_sm = 8;
+    ldpc_tb_kernel<<<sm_count * per_sm, warps * 32, smem, st>>>(p);
+    const int tb_max = p.n_streams * p.tb_slots;
+    tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
+    tb_gather_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
+    carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
+    if (launches) *launches += 6;
+    return cudaGetLastError();
+}
+
+__global__ void cursor_clear_kernel(int* c) { *c = 0; }
+
+cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
+{
+    if (p.count <= 0) return cudaSuccess;
+    const int warps = 8;
+    const size_t smem = (size_t)p.warp_bytes * warps;
+    if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+    static size_t attr_set = 0;
+    if (smem > 48 * 1024 && smem > attr_set) {
+        cudaFuncSetAttribute(ldpc_plain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = smem;
+    }
+    int per_sm = (int)((220 * 1024) / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 8) per_sm = 8;
+    long long want = (p.count + warps - 1) / warps;
+    int blocks = (int)(want < (long long)sm_count * per_sm ? want : (long long)sm_count * per_sm);
+    cursor_clear_kernel<<<1, 1, 0, st>>>(p.cursor);
+    ldpc_plain_kernel<<<blocks, warps * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+} // namespace dtl

@@ -143,6 +143,10 @@ int32_t dtl_b200_bytes_stride(const dtl_b200* h);
 dtl_status dtl_b200_code_info(const dtl_b200* h, int32_t fec_id, int32_t* n, int32_t* k, int32_t* permute);
 /* number of kernels this handle has launched since create (bench.py's gpu_launches) */
 uint64_t dtl_b200_launch_count(const dtl_b200* h);
+/* Page-locked host memory for DTL_MEM_HOST buffers (what a GNU Radio custom buffer would hand to work()):
+ * copies from/to such memory overlap with the kernels of the call; pageable memory works too, slower. */
+dtl_status dtl_b200_host_alloc(void** out, size_t bytes);
+void dtl_b200_host_free(void* p);
 
 /* ---- stage 1: CP strip + FFT ---------------------------------------------------------------------------
  * digital.header_payload_demux(output_symbols=True) + fft.fft_vcc(fft_len, True, (), True) on the payload
