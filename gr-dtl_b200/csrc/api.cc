@@ -37,7 +37,7 @@ struct DevBuf {
 enum Slot {
     SL_IQ, SL_FREQ_IN, SL_TAPS, SL_META, SL_HARD, SL_SOFT, SL_TAPS_OUT, SL_RES, SL_LLR, SL_NLLR, SL_FBYTES, SL_FNBYTES,
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
-    SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT,
+    SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
     SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_BITS, SL_COUNT
 };
@@ -49,6 +49,7 @@ struct dtl_b200 {
     cudaStream_t stream = nullptr;
     std::string err;
     uint64_t launches = 0;
+    Prof prof;
     // configuration (deep copies)
     int N = 0, cp = 0, L = 0, H = 1, cap = 0, max_bps = 0, fec_enabled = 0;
     int llr_stride = 0, bytes_stride = 0, frame_samples = 0;
@@ -137,6 +138,7 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
     h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release();
+    h->prof.release();
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -292,11 +294,16 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
             col_ptr[v + 1] = (uint16_t)col_edge.size();
         }
         for (int q = 0; q < code.n; q++) perm[q] = (uint16_t)code.permute[q];
+        const int kwords = (code.k + 31) / 32;
+        std::vector<uint32_t> pmat((size_t)code.rank * kwords, 0u);
+        for (int r = 0; r < code.rank; r++)
+            for (int j = 0; j < code.k; j++) if (code.P[r][j]) pmat[(size_t)r * kwords + (j >> 5)] |= 1u << (j & 31);
         if (code.max_row > 32) return fail(h, DTL_ERR_UNSUPPORTED, "LDPC row weight > 32");
         CodeDev& d = code.dev;
         d.n = code.n; d.m = code.m; d.k = code.k; d.rank = code.rank; d.edges = code.edges; d.max_row = code.max_row; d.max_col = code.max_col;
         d.row_ptr = h->upload(row_ptr, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
         d.col_edge = h->upload(col_edge, e); d.permute = h->upload(perm, e);
+        d.pmat = h->upload(pmat, e); d.kwords = kwords;
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
         h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, code.edges));
@@ -342,6 +349,7 @@ extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
     if (prop.major != 10) { fail(h, DTL_ERR_UNSUPPORTED, "libdtl_b200 is built for sm_100a only"); return bail(DTL_ERR_UNSUPPORTED); }
     h->sm_count = prop.multiProcessorCount;
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { cuda_fail(h, e, "cudaStreamCreate"); return bail(DTL_ERR_CUDA); }
+    h->prof.st = h->stream;
     h->N = N; h->cp = c->cp_len; h->L = c->frame_len; h->H = c->header_syms > 0 ? c->header_syms : (c->fec_enabled ? 2 : 1);
     h->max_bps = c->max_bps; h->fec_enabled = c->fec_enabled;
     h->ldpc_max_it = c->ldpc_max_iterations > 0 ? c->ldpc_max_iterations : 15;
@@ -368,18 +376,18 @@ extern "C" dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams)
 {
     if (!h || n_streams < 0) return DTL_ERR_INVALID_ARG;
     CK(cudaSetDevice(h->device));
-    CK(cudaStreamSynchronize(h->stream));
-    std::vector<StreamState> st((size_t)n_streams);
-    for (auto& s : st) {
-        memset(&s, 0, sizeof(s));
-        s.fb_last = s.fb_next = h->initial_mcs;      // ofdm_adaptive_feedback_decision.cc:33-53
-        s.tb_number = -1;                             // tb_decoder.cc:21-30
-    }
-    CK(h->st_buf.ensure(std::max<size_t>(st.size() * sizeof(StreamState), 16)));
-    if (n_streams) CK(cudaMemcpy(h->st_buf.p, st.data(), st.size() * sizeof(StreamState), cudaMemcpyHostToDevice));
-    if (h->carry_cap) CK(h->carry_buf.ensure((size_t)n_streams * h->carry_cap * sizeof(float) + 16));
-    CK(h->pend_buf.ensure((size_t)n_streams * sizeof(TbDesc) + 16));
-    CK(cudaMemset(h->d_err, 0, sizeof(int)));
+    // growing a buffer frees the old one: wait for the kernels that may still read it (no-op when sizes are unchanged,
+    // so a reset between batches only enqueues one small kernel on the handle's stream)
+    const size_t st_bytes = std::max<size_t>((size_t)n_streams * sizeof(StreamState), 16);
+    const size_t carry_bytes = h->carry_cap ? (size_t)n_streams * h->carry_cap * sizeof(float) + 16 : 0;
+    const size_t pend_bytes = (size_t)n_streams * sizeof(TbDesc) + 16;
+    if (st_bytes > h->st_buf.cap || carry_bytes > h->carry_buf.cap || pend_bytes > h->pend_buf.cap) CK(cudaStreamSynchronize(h->stream));
+    CK(h->st_buf.ensure(st_bytes));
+    if (carry_bytes) CK(h->carry_buf.ensure(carry_bytes));
+    CK(h->pend_buf.ensure(pend_bytes));
+    CK(launch_stream_reset(h->stream, (StreamState*)h->st_buf.p, n_streams, h->initial_mcs));
+    h->launches += n_streams > 0 ? 1 : 0;
+    CK(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
     h->n_streams = n_streams;
     return DTL_OK;
 }
@@ -422,6 +430,27 @@ extern "C" dtl_status dtl_b200_code_info(const dtl_b200* h, int32_t fec_id, int3
     if (n) *n = c.n;
     if (k) *k = c.k;
     if (permute) for (int i = 0; i < c.n; i++) permute[i] = c.permute[i];
+    return DTL_OK;
+}
+
+extern "C" dtl_status dtl_b200_profile(dtl_b200* h, int enable)
+{
+    if (!h) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    h->prof.collect();
+    h->prof.on = enable != 0;
+    return DTL_OK;
+}
+
+extern "C" dtl_status dtl_b200_stage_times(dtl_b200* h, double* ms, int64_t* launches, int32_t n, int reset)
+{
+    if (!h || n < 0 || n > DTL_STAGE_COUNT) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    h->prof.collect();
+    for (int i = 0; i < n; i++) { if (ms) ms[i] = h->prof.ms[i]; if (launches) launches[i] = h->prof.n[i]; }
+    if (reset) for (int i = 0; i < DTL_STAGE_COUNT; i++) { h->prof.ms[i] = 0; h->prof.n[i] = 0; }
     return DTL_OK;
 }
 
@@ -498,7 +527,9 @@ namespace {
 
 dtl_status dev_demod(dtl_b200* h, const float2* iq, long long n_frames, float2* freq)
 {
+    h->prof.begin(DTL_STAGE_FFT, 1);
     CK(launch_fft_fwd(h->stream, iq, freq, n_frames * h->L, h->L, h->frame_samples, h->H + 2, h->N + h->cp, h->cp, h->N, h->tw));
+    h->prof.end();
     h->launches += 1;
     return DTL_OK;
 }
@@ -517,12 +548,16 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr;
     p.bytes = fbytes; p.bytes_stride = h->bytes_stride; p.nbytes = fnbytes; p.crc_ok = fcrc;
     p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
+    h->prof.begin(DTL_STAGE_EQ, 1);
     CK(launch_eq(h->stream, p));
+    h->prof.end();
     StreamParams sp;
     sp.st = (StreamState*)h->st_buf.p; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
     sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
     sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
+    h->prof.begin(DTL_STAGE_STATE, 1);
     CK(launch_stream_state(h->stream, sp));
+    h->prof.end();
     h->launches += 2;
     return DTL_OK;
 }
@@ -556,7 +591,7 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     p.bytes = bytes; p.bytes_cap = bytes_cap; p.nbytes = nbytes; p.tb_out = tbs; p.tb_cap = tb_cap; p.ntbs = ntbs;
     p.crc_table = h->crc_table; p.err = h->d_err;
     int launches = 0;
-    CK(launch_fec(h->stream, p, h->sm_count, &launches));
+    CK(launch_fec(h->stream, p, h->sm_count, &launches, &h->prof));
     h->launches += launches;
     return DTL_OK;
 }
@@ -585,8 +620,10 @@ extern "C" dtl_status dtl_b200_fft(dtl_b200* h, const float* in, int64_t n_vec, 
     const float2* d_in = sg.in(SL_FFT_IN, (const float2*)in, (size_t)n_vec * h->N);
     float2* d_out = sg.out(SL_FFT_OUT, (float2*)out, (size_t)n_vec * h->N);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    h->prof.begin(DTL_STAGE_FFT, 1);
     if (forward) CK(launch_fft_fwd(h->stream, d_in, d_out, n_vec, 1, h->N, 0, h->N, 0, h->N, h->tw));
     else CK(launch_fft_inv(h->stream, d_in, d_out, n_vec, h->N, h->tw));
+    h->prof.end();
     h->launches += 1;
     return sg.finish();
 }
@@ -647,7 +684,9 @@ static dtl_status demap_common(dtl_b200* h, int mode, const float* syms, const u
     p.chunks = sg.out(SL_BITS_OUT, chunks, n * stride_syms);
     p.out_syms = sg.out(SL_SOFT, (float2*)out_syms, n * stride_syms);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    h->prof.begin(DTL_STAGE_DEMAP, 1);
     CK(launch_demap(h->stream, p));
+    h->prof.end();
     h->launches += 1;
     return sg.finish();
 }
@@ -712,8 +751,28 @@ extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const fl
     p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
     p.nit = sg.out(SL_NIT, nit, (size_t)count);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    h->prof.begin(DTL_STAGE_LDPC, 2);
     CK(launch_ldpc(h->stream, p, h->sm_count));
+    h->prof.end();
     h->launches += 2;
+    return sg.finish();
+}
+
+// ldpc_enc::encode for `count` blocks (TX side of the loopback; lib/dtl/ldpc_enc.cc:58-68)
+extern "C" dtl_status dtl_b200_ldpc_encode(dtl_b200* h, int32_t fec_id, const uint8_t* data, int64_t count, uint8_t* wire, int mem)
+{
+    if (!h || !data || !wire || count < 0) return DTL_ERR_INVALID_ARG;
+    if (fec_id < 1 || fec_id >= (int)h->codes.size()) return fail(h, DTL_ERR_MISSING_TAG, "FEC tags missing");
+    CK(cudaSetDevice(h->device));
+    const Code& c = h->codes[fec_id];
+    Stage sg(h, mem);
+    const uint8_t* d_in = sg.in(SL_ENC_IN, data, (size_t)count * c.k);
+    uint8_t* d_out = sg.out(SL_ENC_OUT, wire, (size_t)count * c.n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    h->prof.begin(DTL_STAGE_TX, 1);
+    CK(launch_ldpc_encode(h->stream, c.dev, d_in, count, d_out));
+    h->prof.end();
+    h->launches += 1;
     return sg.finish();
 }
 
@@ -764,7 +823,9 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
         s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, nullptr, nullptr, fb, fnb, d_fcrc);
         if (s != DTL_OK) return s;
         if (d_bytes || d_nb) {
+            h->prof.begin(DTL_STAGE_TBFINISH, 1);
             CK(launch_frame_gather(h->stream, fb, h->bytes_stride, fnb, S, F, d_bytes, d_bytes ? bytes_cap : 0, d_nb, h->d_err));
+            h->prof.end();
             h->launches += 1;
         }
         if (d_nt) CK(cudaMemsetAsync(d_nt, 0, (size_t)S * sizeof(int), h->stream));
@@ -794,7 +855,9 @@ extern "C" dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const ui
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
     p.sync1 = h->d_sync1; p.sync2 = h->d_sync2; p.ser_pos = h->pl.ser_pos; p.tx_base = h->d_tx_base;
     p.tx_pil_mask = h->d_tx_pil_mask; p.tx_pil_val = h->d_tx_pil_val; p.tw = h->tw; p.cn = h->cn;
+    h->prof.begin(DTL_STAGE_TX, 1);
     CK(launch_tx_mod(h->stream, p));
+    h->prof.end();
     h->launches += 1;
     return sg.finish();
 }

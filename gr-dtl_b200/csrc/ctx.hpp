@@ -46,6 +46,8 @@ struct CodeDev {
     const uint16_t* col_ptr;     // [n+1]
     const uint16_t* col_edge;    // [edges] edge ids of variable v in nlist order
     const uint16_t* permute;     // [n]
+    const uint32_t* pmat;        // [rank][kwords] parity part of the systematic generator, bit j of row i = P[i][j]
+    int kwords;                  // ceil(k / 32)
 };
 
 // Per-stream receiver state that survives between calls.
@@ -81,6 +83,45 @@ struct Code {                    // host copy
 };
 
 bool load_alist(const std::string& path, Code& c, std::string& err);
+
+// Per-stage device timer (dtl_b200_profile / dtl_b200_stage_times): event pairs on the handle's stream.
+struct Prof {
+    bool on = false;
+    cudaStream_t st = nullptr;
+    struct Rec { int stage; int launches; cudaEvent_t a, b; };
+    std::vector<Rec> pending;
+    std::vector<cudaEvent_t> pool;
+    double ms[DTL_STAGE_COUNT] = { 0 };
+    long long n[DTL_STAGE_COUNT] = { 0 };
+    cudaEvent_t get()
+    {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+    }
+    void begin(int stage, int launches)
+    {
+        if (!on) return;
+        Rec r; r.stage = stage; r.launches = launches; r.a = get(); r.b = get();
+        cudaEventRecord(r.a, st);
+        pending.push_back(r);
+    }
+    void end() { if (on && !pending.empty()) cudaEventRecord(pending.back().b, st); }
+    void collect()                       // the stream must be idle
+    {
+        for (auto& r : pending) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ms[r.stage] += t; n[r.stage] += r.launches; }
+            pool.push_back(r.a); pool.push_back(r.b);
+        }
+        pending.clear();
+    }
+    void release()
+    {
+        for (auto& r : pending) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        for (auto e : pool) cudaEventDestroy(e);
+        pending.clear(); pool.clear();
+    }
+};
 
 // host constellation tables (lib/dtl/ofdm_adaptive_utils.cc:41-70, lib/dtl/constellation.cc:18-24)
 int cnst_bps(int c);

@@ -81,10 +81,12 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
 cudaError_t launch_fft_inv(cudaStream_t st, const float2* in, float2* out, long long n_sym, int N, const float2* tw);
 cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p);
 cudaError_t launch_eq(cudaStream_t st, const EqParams& p);
+cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
-cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches);
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof);
 size_t ldpc_warp_bytes(int n, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
+cudaError_t launch_ldpc_encode(cudaStream_t st, const CodeDev& code, const uint8_t* data, long long count, uint8_t* wire);
 cudaError_t launch_demap(cudaStream_t st, const DemapParams& p);   // mode 0 soft, 1 hard, 2 map
 cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int bytes_stride, const int* fn, int n_streams, int F,
                                 uint8_t* out, int cap, int* out_n, int* err);

@@ -427,11 +427,14 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
 
 __global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = 0; *bits_used = 0ull; }
 
-cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches)
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof)
 {
     if (p.n_streams <= 0 || p.F <= 0) return cudaSuccess;
+    Prof none; if (!prof) prof = &none;
+    prof->begin(DTL_STAGE_TBPLAN, 2);
     fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
     tb_plan_kernel<<<(p.n_streams + 127) / 128, 128, 0, st>>>(p);
+    prof->end();
     const int warps = 8;
     const size_t smem = (size_t)p.warp_bytes * warps;
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
@@ -443,11 +446,15 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     int per_sm = (int)((220 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 8) per_sm = 8;
+    prof->begin(DTL_STAGE_LDPC, 1);
     ldpc_tb_kernel<<<sm_count * per_sm, warps * 32, smem, st>>>(p);
+    prof->end();
     const int tb_max = p.n_streams * p.tb_slots;
+    prof->begin(DTL_STAGE_TBFINISH, 3);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
     tb_gather_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
+    prof->end();
     if (launches) *launches += 6;
     return cudaGetLastError();
 }
@@ -472,6 +479,46 @@ cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
     int blocks = (int)(want < (long long)sm_count * per_sm ? want : (long long)sm_count * per_sm);
     cursor_clear_kernel<<<1, 1, 0, st>>>(p.cursor);
     ldpc_plain_kernel<<<blocks, warps * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+// ---- ldpc_enc::encode (lib/dtl/ldpc_enc.cc:58-68; gr-fec cldpc::encode) -------------------------------------------
+// Systematic encode of `count` blocks of k bits (one bit per byte): parity[i] = P[i] . data over GF(2); the wire
+// order after gr-dtl's un-permute (ldpc_enc.cc:65-67) is [parity(rank) | data(k)].  One warp per codeword: the k
+// data bits become kwords ballot words in shared memory, each lane then owns parity rows lane, lane+32, ...
+__global__ void __launch_bounds__(256) ldpc_encode_kernel(CodeDev c, const uint8_t* __restrict__ data, long long count,
+                                                           uint8_t* __restrict__ wire)
+{
+    extern __shared__ uint32_t encw[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t* dw = encw + wid * c.kwords;
+    const long long cw = (long long)blockIdx.x * (blockDim.x >> 5) + wid;
+    if (cw >= count) return;
+    const uint8_t* in = data + cw * c.k;
+    uint8_t* out = wire + cw * c.n;
+    for (int w = 0; w < c.kwords; w++) {
+        const int j = w * 32 + lane;
+        const unsigned bit = j < c.k ? (in[j] & 1u) : 0u;
+        const uint32_t word = __ballot_sync(0xffffffffu, bit);
+        if (lane == 0) dw[w] = word;
+        if (j < c.k) out[c.rank + j] = (uint8_t)bit;
+    }
+    __syncwarp();
+    for (int i = lane; i < c.rank; i += 32) {
+        const uint32_t* row = c.pmat + (size_t)i * c.kwords;
+        uint32_t acc = 0;
+        for (int w = 0; w < c.kwords; w++) acc ^= __ldg(&row[w]) & dw[w];
+        out[i] = (uint8_t)(__popc(acc) & 1);
+    }
+}
+
+cudaError_t launch_ldpc_encode(cudaStream_t st, const CodeDev& code, const uint8_t* data, long long count, uint8_t* wire)
+{
+    if (count <= 0) return cudaSuccess;
+    const int warps = 8;
+    const long long blocks = (count + warps - 1) / warps;
+    if (blocks > 0x7fffffffLL) return cudaErrorInvalidValue;
+    ldpc_encode_kernel<<<(unsigned)blocks, warps * 32, (size_t)warps * code.kwords * 4, st>>>(code, data, count, wire);
     return cudaGetLastError();
 }
 

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libdtl_b200.so")
 OK, ERR_INVALID_ARG, ERR_MISSING_TAG, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_CAPACITY, ERR_IO = range(8)
 MEM_HOST, MEM_DEVICE = 0, 1
 LDPC_REFERENCE, LDPC_LAYERED = 0, 1
+STAGES = ("fft", "eq_demap", "stream_state", "tb_plan", "ldpc", "tb_finish", "tx", "demap")
 
 frame_meta_dtype = np.dtype([
     ("constellation", "<i4"), ("carrier_offset", "<i4"), ("frame_no", "<i4"), ("payload_len", "<i4"),
@@ -50,8 +51,9 @@ SYMBOLS = (
     "dtl_b200_abi_version", "dtl_b200_create", "dtl_b200_destroy", "dtl_b200_last_error", "dtl_b200_reset",
     "dtl_b200_sync", "dtl_b200_cuda_stream", "dtl_b200_frame_capacity", "dtl_b200_frame_samples",
     "dtl_b200_llr_stride", "dtl_b200_bytes_stride", "dtl_b200_code_info", "dtl_b200_launch_count",
+    "dtl_b200_profile", "dtl_b200_stage_times",
     "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize",
-    "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode",
+    "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode",
     "dtl_b200_rx", "dtl_b200_tx")
 
 _lib = None
@@ -88,6 +90,8 @@ def lib():
         L.dtl_b200_code_info.argtypes = [vp, i32, _i32p, _i32p, vp]
         L.dtl_b200_launch_count.argtypes = [vp]
         L.dtl_b200_launch_count.restype = C.c_uint64
+        L.dtl_b200_profile.argtypes = [vp, C.c_int]
+        L.dtl_b200_stage_times.argtypes = [vp, vp, vp, i32, C.c_int]
         L.dtl_b200_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.dtl_b200_host_free.argtypes = [vp]
         L.dtl_b200_host_free.restype = None
@@ -99,6 +103,7 @@ def lib():
         L.dtl_b200_map.argtypes = [vp, vp, i32, vp, i64, vp, C.c_int]
         L.dtl_b200_fec_decode.argtypes = [vp, vp, i32, vp, i32, i32, vp, i32, vp, vp, i32, vp, C.c_int]
         L.dtl_b200_ldpc_decode.argtypes = [vp, i32, vp, i64, vp, vp, C.c_int]
+        L.dtl_b200_ldpc_encode.argtypes = [vp, i32, vp, i64, vp, C.c_int]
         L.dtl_b200_rx.argtypes = [vp, C.c_int, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         L.dtl_b200_tx.argtypes = [vp, vp, vp, vp, i64, vp, C.c_int]
         _lib = L

@@ -121,6 +121,7 @@ class ofdm_receiver:
         if st != _capi.OK:
             raise DtlError(st, (self._lib.dtl_b200_last_error(None) or b"").decode())
         self._h = h
+        self._pinned = []
         self.device = device
         self.frame_capacity = self._lib.dtl_b200_frame_capacity(h)
         assert self.frame_capacity == frame_capacity(self.frame_length, occ)
@@ -133,6 +134,9 @@ class ofdm_receiver:
         if getattr(self, "_h", None):
             self._lib.dtl_b200_destroy(self._h)
             self._h = None
+            for p in self._pinned:
+                self._lib.dtl_b200_host_free(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -149,6 +153,30 @@ class ofdm_receiver:
 
     def sync(self):
         self._ck(self._lib.dtl_b200_sync(self._h))
+
+    def profile(self, enable=True):
+        """bracket every stage's kernels with CUDA events on the handle's stream (dtl_b200_profile)"""
+        self._ck(self._lib.dtl_b200_profile(self._h, int(enable)))
+
+    def stage_times(self, reset=True):
+        """{stage: (milliseconds, kernel launches)} accumulated since the last reset (dtl_b200_stage_times)"""
+        n = len(_capi.STAGES)
+        ms, cnt = np.zeros(n, dtype=np.float64), np.zeros(n, dtype=np.int64)
+        self._ck(self._lib.dtl_b200_stage_times(self._h, ms.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p), n,
+                                                int(reset)))
+        return {k: (float(ms[i]), int(cnt[i])) for i, k in enumerate(_capi.STAGES)}
+
+    def host_alloc(self, shape, dtype):
+        """page-locked NumPy array (dtl_b200_host_alloc); freed with the receiver"""
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        p = C.c_void_p()
+        st = self._lib.dtl_b200_host_alloc(C.byref(p), max(nbytes, 1))
+        if st != _capi.OK:
+            raise DtlError(st, "dtl_b200_host_alloc failed")
+        self._pinned.append(p)
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(p.value)
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
     @property
     def launch_count(self):
@@ -280,6 +308,15 @@ class ofdm_receiver:
         nit = self._new(a.mem, (count,), np.int32)
         self._ck(self._lib.dtl_b200_ldpc_decode(self._h, fec_id, a.ptr, count, _Arg(bits).ptr, _Arg(nit).ptr, a.mem))
         return bits, nit
+
+    def ldpc_encode(self, fec_id, data):
+        """ldpc_enc::encode for a batch: data bits [count, k] -> wire bits [count, n] = [parity | data]"""
+        a = _Arg(data)
+        count = data.shape[0]
+        info = self.code_info(fec_id)
+        out = self._new(a.mem, (count, info["N"]), np.uint8)
+        self._ck(self._lib.dtl_b200_ldpc_encode(self._h, fec_id, a.ptr, count, _Arg(out).ptr, a.mem))
+        return out
 
     # ---- the whole payload branch ------------------------------------------------------------------------------
     def rx(self, inp, taps, meta, n_streams, frames_per_stream, freq_domain=False, out=None, bytes_cap=None, tb_cap=None):

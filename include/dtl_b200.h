@@ -143,6 +143,13 @@ int32_t dtl_b200_bytes_stride(const dtl_b200* h);
 dtl_status dtl_b200_code_info(const dtl_b200* h, int32_t fec_id, int32_t* n, int32_t* k, int32_t* permute);
 /* number of kernels this handle has launched since create (bench.py's gpu_launches) */
 uint64_t dtl_b200_launch_count(const dtl_b200* h);
+/* Per-stage device time.  While enabled the handle brackets every stage's kernels with CUDA events on its own
+ * stream; dtl_b200_stage_times waits for the stream and returns, per stage, the accumulated milliseconds and
+ * the number of kernel launches since the last reset (ms / launches may be NULL; n <= DTL_STAGE_COUNT). */
+enum { DTL_STAGE_FFT = 0, DTL_STAGE_EQ = 1, DTL_STAGE_STATE = 2, DTL_STAGE_TBPLAN = 3, DTL_STAGE_LDPC = 4,
+       DTL_STAGE_TBFINISH = 5, DTL_STAGE_TX = 6, DTL_STAGE_DEMAP = 7, DTL_STAGE_COUNT = 8 };
+dtl_status dtl_b200_profile(dtl_b200* h, int enable);
+dtl_status dtl_b200_stage_times(dtl_b200* h, double* ms, int64_t* launches, int32_t n, int reset);
 /* Page-locked host memory for DTL_MEM_HOST buffers (what a GNU Radio custom buffer would hand to work()):
  * copies from/to such memory overlap with the kernels of the call; pageable memory works too, slower. */
 dtl_status dtl_b200_host_alloc(void** out, size_t bytes);
@@ -210,6 +217,10 @@ dtl_status dtl_b200_fec_decode(dtl_b200* h, const float* llr, int32_t llr_stride
  * `count` codewords per call: llr f32 [count][n] wire order, bits u8 [count][k], nit i32 [count]. */
 dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const float* llr, int64_t count,
                                 uint8_t* bits, int32_t* nit, int mem);
+
+/* fec_enc::encode(const unsigned char* in_data, int len, unsigned char* out_data) (include/gnuradio/dtl/fec.h:17-23; ldpc_enc::encode lib/dtl/ldpc_enc.cc:58-68)
+ * for `count` blocks: data u8 [count][k] one bit per byte -> wire u8 [count][n] = [parity (n-k) | data (k)]. */
+dtl_status dtl_b200_ldpc_encode(dtl_b200* h, int32_t fec_id, const uint8_t* data, int64_t count, uint8_t* wire, int mem);
 
 /* ---- the whole receive path (stages 1-4 back to back, intermediates stay in HBM) -----------------------------
  * in_kind 0: iq c64 [S*F][frame_samples]; 1: freq c64 [S*F][frame_len][fft_len] (stage 1 skipped).
