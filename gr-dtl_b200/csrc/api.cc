@@ -223,6 +223,22 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
     pl.occupied = h->upload(occupied, e); pl.pilot_mask = h->upload(pmask, e); pl.pilot_rank = h->upload(prank, e);
     pl.pilot_prefix = h->upload(pprefix, e); pl.pilot_sym = h->upload(psym, e); pl.pilot_inv = h->upload(pinv, e);
     pl.ser_pos = h->upload(ser_pos, e); pl.ser_base = h->upload(ser_base, e); pl.phase_tab = h->upload(ptab, e);
+    // per (symbol, bin) role and the inverse of the serialiser (eq_demap_kernel phases 1 and 2)
+    if ((size_t)L * N > 65535 || pprefix[L] > 65535) return fail(h, DTL_ERR_UNSUPPORTED, "frame_len * fft_len > 65535");
+    std::vector<uint32_t> sym_kind((size_t)L * N, 0u);
+    std::vector<uint16_t> ser_src((size_t)std::max(h->cap, 1), 0);
+    for (int i = 0; i < L; i++) {
+        const int pcs = npc ? (pl.pcs0 + i) % npc : 0;
+        for (int b = 0; b < N; b++) {
+            uint32_t v = 0;
+            if (npc && pmask[(size_t)pcs * N + b]) v = 2u | ((uint32_t)(pprefix[i] + prank[(size_t)pcs * N + b]) << 16);
+            else if (occupied[b]) v = 1u;
+            sym_kind[(size_t)i * N + b] = v;
+        }
+        const int oset = (1 + i) % nocc;
+        for (size_t k = 0; k < occ[oset].size(); k++) ser_src[ser_base[i] + k] = (uint16_t)(i * N + bin_of(occ[oset][k], N, shifted));
+    }
+    pl.sym_kind = h->upload(sym_kind, e); pl.ser_src = h->upload(ser_src, e);
 
     // ---- TX allocator tables (digital.ofdm_carrier_allocator_cvc): data symbol s = 0 is the first header symbol
     std::vector<int> tx_base(H + L + 1, 0);

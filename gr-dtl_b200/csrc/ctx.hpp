@@ -36,6 +36,8 @@ struct PlanDev {
     const int16_t* ser_pos;      // [nocc][N] serialiser position of bin in set, -1 = not in set
     const int* ser_base;         // [L+1] serialised symbols before OFDM symbol i
     const float2* phase_tab;     // [2*max_off+1][L+1]: per-symbol correction i<L, taps rotation at L
+    const uint32_t* sym_kind;    // [L][N] bits 0-1: 0 unused / 1 data / 2 pilot; bits 16-31: pilot slot in the frame
+    const uint16_t* ser_src;     // [cap] serialised symbol idx -> i*N + bin
 };
 
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.

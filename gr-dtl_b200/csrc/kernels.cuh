@@ -30,8 +30,8 @@ struct EqParams {
     uint8_t* bytes; int bytes_stride; int* nbytes; int* crc_ok;
     const uint32_t* crc_table;                     // [256] reflected CRC-32
     int* err;                                      // device error word (bit 0: bad constellation)
-    // fused stage 1 (in_kind 0): time-domain IQ instead of freq
-    const float2* iq; int frame_samples, cp, sym0; const float2* tw;
+    const float2* tw;
+    int use_tma;                                   // set by the launcher: source 16-byte aligned
 };
 
 // ---- per-stream sequential bookkeeping ------------------------------------------------------------------
