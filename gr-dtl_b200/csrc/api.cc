@@ -74,6 +74,11 @@ struct dtl_b200 {
     int* d_err = nullptr; int* d_cnt = nullptr; unsigned long long* d_bits_used = nullptr; int* d_cursor = nullptr;
     int* h_err = nullptr;             // pinned mirror of d_err
     DevBuf slot[SL_COUNT];
+    // pipelined DTL_MEM_HOST receive path: chunks of streams, H2D of chunk c+1 under the kernels of chunk c
+    cudaStream_t copy_stream = nullptr, out_stream = nullptr;
+    cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_done[2] = { nullptr, nullptr };
+    DevBuf pipe_in[2][3];
+    int s_off = 0;                    // first stream of the chunk the device-level stages work on
 
     template <class T> T* upload(const std::vector<T>& v, cudaError_t& e)
     {
@@ -139,6 +144,13 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     for (auto& b : h->slot) b.release();
     h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release();
     h->prof.release();
+    for (int i = 0; i < 2; i++) {
+        if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
+        if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+        for (auto& b : h->pipe_in[i]) b.release();
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->out_stream) cudaStreamDestroy(h->out_stream);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -568,7 +580,7 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     CK(launch_eq(h->stream, p));
     h->prof.end();
     StreamParams sp;
-    sp.st = (StreamState*)h->st_buf.p; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
+    sp.st = (StreamState*)h->st_buf.p + h->s_off; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
     sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
     sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
     h->prof.begin(DTL_STAGE_STATE, 1);
@@ -585,14 +597,14 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     FecParams p;
     memset(&p, 0, sizeof p);
     const size_t tb_slots = 2 * (size_t)F + 1, budget = (size_t)S * ((size_t)F + 2);
-    p.st = (StreamState*)h->st_buf.p; p.n_streams = S; p.F = F; p.meta = meta; p.llr = llr; p.llr_stride = llr_stride;
-    p.carry = (float*)h->carry_buf.p; p.carry_cap = h->carry_cap;
+    p.st = (StreamState*)h->st_buf.p + h->s_off; p.n_streams = S; p.F = F; p.meta = meta; p.llr = llr; p.llr_stride = llr_stride;
+    p.carry = (float*)h->carry_buf.p + (size_t)h->s_off * h->carry_cap; p.carry_cap = h->carry_cap;
     p.n_codes = (int)h->codes.size() - 1; p.codes = h->d_codes; p.cap = h->cap;
     for (int c = 0; c <= DTL_CNST_MAX; c++) p.bps_tab[c] = cnst_bps(c);
     p.max_tb = h->max_tb;
     p.tb_slots = (int)tb_slots;
     p.tbs = sg.scratch<TbDesc>(SL_TBDESC, (size_t)S * tb_slots);
-    p.pend = (TbDesc*)h->pend_buf.p;
+    p.pend = (TbDesc*)h->pend_buf.p + h->s_off;
     p.tres = sg.scratch<dtl_tb_result>(SL_TRES, (size_t)S * tb_slots);
     p.tb_count = sg.scratch<int>(SL_TBCOUNT, (size_t)S);
     p.tb_list = sg.scratch<int>(SL_TBLIST, (size_t)S * tb_slots);
@@ -793,6 +805,116 @@ extern "C" dtl_status dtl_b200_ldpc_encode(dtl_b200* h, int32_t fec_id, const ui
 }
 
 // ---- the whole receive path ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+// stages 1-4 on device pointers for S streams x F frames (the streams [h->s_off, h->s_off + S) of the handle's state)
+dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, const float2* d_taps, const dtl_frame_meta* d_meta,
+                     int S, int F, dtl_frame_result* d_res, uint8_t* d_bytes, int bytes_cap, int* d_nb,
+                     dtl_tb_result* d_tbs, int tb_cap, int* d_nt, int* d_fcrc)
+{
+    const size_t n = (size_t)S * F, LN = (size_t)h->L * h->N;
+    dtl_status s;
+    const float2* d_freq = d_in;
+    if (in_kind == 0) {
+        float2* fq = sg.scratch<float2>(SL_FREQ, n * LN);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        if ((s = dev_demod(h, d_in, (long long)n, fq)) != DTL_OK) return s;
+        d_freq = fq;
+    }
+    if (h->fec_enabled) {
+        float* d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
+        if (s != DTL_OK) return s;
+        return dev_fec(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt);
+    }
+    uint8_t* fb = sg.scratch<uint8_t>(SL_FBYTES, n * h->bytes_stride);
+    int* fnb = sg.scratch<int>(SL_FNBYTES, n);
+    if (!d_fcrc) d_fcrc = sg.scratch<int>(SL_FCRC, n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, nullptr, nullptr, fb, fnb, d_fcrc);
+    if (s != DTL_OK) return s;
+    if (d_bytes || d_nb) {
+        h->prof.begin(DTL_STAGE_TBFINISH, 1);
+        CK(launch_frame_gather(h->stream, fb, h->bytes_stride, fnb, S, F, d_bytes, d_bytes ? bytes_cap : 0, d_nb, h->d_err));
+        h->prof.end();
+        h->launches += 1;
+    }
+    if (d_nt) CK(cudaMemsetAsync(d_nt, 0, (size_t)S * sizeof(int), h->stream));
+    return DTL_OK;
+}
+
+// DTL_MEM_HOST with many streams: the batch is cut into chunks of whole streams (streams are independent; the
+// per-stream state is indexed by stream).  Chunk c+1's host->device copies run on the copy stream under chunk c's
+// kernels, the small device->host result copies of chunk c on a third stream; two input staging buffers alternate.
+dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
+                             int S, int F, int Sc, dtl_frame_result* res, uint8_t* bytes, int bytes_cap, int* nbytes,
+                             dtl_tb_result* tbs, int tb_cap, int* ntbs, int* frame_crc)
+{
+    if (!h->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            CK(cudaEventCreateWithFlags(&h->ev_h2d[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    const size_t in_per_frame = in_kind == 0 ? (size_t)h->frame_samples : (size_t)h->L * h->N;
+    const size_t nmax = (size_t)Sc * F;
+    Stage sg(h, DTL_MEM_DEVICE);
+    // full-batch device outputs (small), per-chunk inputs (double-buffered)
+    dtl_frame_result* d_res = res ? sg.scratch<dtl_frame_result>(SL_RES, (size_t)S * F) : nullptr;
+    uint8_t* d_bytes = bytes ? sg.scratch<uint8_t>(SL_BYTES, (size_t)S * bytes_cap) : nullptr;
+    int* d_nb = nbytes ? sg.scratch<int>(SL_NBYTES, (size_t)S) : nullptr;
+    dtl_tb_result* d_tbs = tbs ? sg.scratch<dtl_tb_result>(SL_TBS_OUT, (size_t)S * tb_cap) : nullptr;
+    int* d_nt = ntbs ? sg.scratch<int>(SL_NTBS, (size_t)S) : nullptr;
+    int* d_fcrc = frame_crc ? sg.scratch<int>(SL_FCRC, (size_t)S * F) : nullptr;
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    for (int i = 0; i < 2; i++) {
+        CK(h->pipe_in[i][0].ensure(nmax * in_per_frame * sizeof(float2) + 16));
+        CK(h->pipe_in[i][1].ensure(nmax * h->N * sizeof(float2) + 16));
+        CK(h->pipe_in[i][2].ensure(nmax * sizeof(dtl_frame_meta) + 16));
+    }
+    // the copy stream must not overtake work already queued on the handle's stream (e.g. dtl_b200_reset)
+    CK(cudaEventRecord(h->ev_done[0], h->stream));
+    CK(cudaStreamWaitEvent(h->copy_stream, h->ev_done[0], 0));
+    CK(cudaStreamWaitEvent(h->out_stream, h->ev_done[0], 0));
+    dtl_status s = DTL_OK;
+    int c = 0;
+    for (int s0 = 0; s0 < S && s == DTL_OK; s0 += Sc, c++) {
+        const int Sn = std::min(Sc, S - s0), b = c & 1;
+        const size_t f0 = (size_t)s0 * F, n = (size_t)Sn * F;
+        if (c >= 2) CK(cudaStreamWaitEvent(h->copy_stream, h->ev_done[b], 0));     // staging buffer b is free again
+        CK(cudaMemcpyAsync(h->pipe_in[b][0].p, (const float2*)in + f0 * in_per_frame, n * in_per_frame * sizeof(float2), cudaMemcpyHostToDevice, h->copy_stream));
+        CK(cudaMemcpyAsync(h->pipe_in[b][1].p, (const float2*)taps + f0 * h->N, n * h->N * sizeof(float2), cudaMemcpyHostToDevice, h->copy_stream));
+        CK(cudaMemcpyAsync(h->pipe_in[b][2].p, meta + f0, n * sizeof(dtl_frame_meta), cudaMemcpyHostToDevice, h->copy_stream));
+        CK(cudaEventRecord(h->ev_h2d[b], h->copy_stream));
+        CK(cudaStreamWaitEvent(h->stream, h->ev_h2d[b], 0));
+        h->s_off = s0;
+        s = rx_device(h, sg, in_kind, (const float2*)h->pipe_in[b][0].p, (const float2*)h->pipe_in[b][1].p,
+                      (const dtl_frame_meta*)h->pipe_in[b][2].p, Sn, F, d_res ? d_res + f0 : nullptr,
+                      d_bytes ? d_bytes + (size_t)s0 * bytes_cap : nullptr, bytes_cap, d_nb ? d_nb + s0 : nullptr,
+                      d_tbs ? d_tbs + (size_t)s0 * tb_cap : nullptr, tb_cap, d_nt ? d_nt + s0 : nullptr, d_fcrc ? d_fcrc + f0 : nullptr);
+        h->s_off = 0;
+        if (s != DTL_OK) break;
+        CK(cudaEventRecord(h->ev_done[b], h->stream));
+        CK(cudaStreamWaitEvent(h->out_stream, h->ev_done[b], 0));
+        if (res) CK(cudaMemcpyAsync(res + f0, d_res + f0, n * sizeof(dtl_frame_result), cudaMemcpyDeviceToHost, h->out_stream));
+        if (bytes) CK(cudaMemcpyAsync(bytes + (size_t)s0 * bytes_cap, d_bytes + (size_t)s0 * bytes_cap, (size_t)Sn * bytes_cap, cudaMemcpyDeviceToHost, h->out_stream));
+        if (nbytes) CK(cudaMemcpyAsync(nbytes + s0, d_nb + s0, (size_t)Sn * sizeof(int), cudaMemcpyDeviceToHost, h->out_stream));
+        if (tbs) CK(cudaMemcpyAsync(tbs + (size_t)s0 * tb_cap, d_tbs + (size_t)s0 * tb_cap, (size_t)Sn * tb_cap * sizeof(dtl_tb_result), cudaMemcpyDeviceToHost, h->out_stream));
+        if (ntbs) CK(cudaMemcpyAsync(ntbs + s0, d_nt + s0, (size_t)Sn * sizeof(int), cudaMemcpyDeviceToHost, h->out_stream));
+        if (frame_crc) CK(cudaMemcpyAsync(frame_crc + f0, d_fcrc + f0, n * sizeof(int), cudaMemcpyDeviceToHost, h->out_stream));
+    }
+    cudaError_t e1 = cudaStreamSynchronize(h->copy_stream), e2 = cudaStreamSynchronize(h->out_stream);
+    dtl_status s2 = dtl_b200_sync(h);
+    if (e1 != cudaSuccess) return cuda_fail(h, e1, "copy stream");
+    if (e2 != cudaSuccess) return cuda_fail(h, e2, "result stream");
+    return s != DTL_OK ? s : s2;
+}
+
+} // namespace
+
 extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
                                   int32_t n_streams, int32_t frames_per_stream, dtl_frame_result* res,
                                   uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
@@ -806,6 +928,15 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
     dtl_status s = check_meta_host(h, meta, (long long)n, mem);
     if (s != DTL_OK) return s;
     if ((s = ensure_streams(h, S)) != DTL_OK) return s;
+    if (mem == DTL_MEM_HOST && F > 0) {
+        // chunks of about 48 MB of input, at least 4 of them
+        const size_t per_stream = (size_t)F * (in_kind == 0 ? (size_t)h->frame_samples : LN) * sizeof(float2);
+        int Sc = (int)std::max<size_t>(1, ((size_t)48 << 20) / std::max<size_t>(per_stream, 1));
+        if (S >= 4 * Sc || (S >= 8 && per_stream * S >= ((size_t)16 << 20))) {
+            Sc = std::min(Sc, (S + 3) / 4);
+            return rx_host_pipelined(h, in_kind, in, taps, meta, S, F, Sc, res, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, frame_crc);
+        }
+    }
     Stage sg(h, mem);
     const float2* d_in = in_kind == 0 ? sg.in(SL_IQ, (const float2*)in, n * h->frame_samples) : sg.in(SL_FREQ_IN, (const float2*)in, n * LN);
     const float2* d_taps = sg.in(SL_TAPS, (const float2*)taps, n * h->N);
@@ -816,36 +947,9 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
     dtl_tb_result* d_tbs = sg.out(SL_TBS_OUT, tbs, (size_t)S * tb_cap);
     int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
     int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
-    const float2* d_freq = d_in;
-    if (in_kind == 0) {
-        float2* fq = sg.scratch<float2>(SL_FREQ, n * LN);
-        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-        if ((s = dev_demod(h, d_in, (long long)n, fq)) != DTL_OK) return s;
-        d_freq = fq;
-    }
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-    if (h->fec_enabled) {
-        float* d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
-        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
-        if (s != DTL_OK) return s;
-        s = dev_fec(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt);
-        if (s != DTL_OK) return s;
-    } else {
-        uint8_t* fb = sg.scratch<uint8_t>(SL_FBYTES, n * h->bytes_stride);
-        int* fnb = sg.scratch<int>(SL_FNBYTES, n);
-        if (!d_fcrc) d_fcrc = sg.scratch<int>(SL_FCRC, n);
-        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, nullptr, nullptr, fb, fnb, d_fcrc);
-        if (s != DTL_OK) return s;
-        if (d_bytes || d_nb) {
-            h->prof.begin(DTL_STAGE_TBFINISH, 1);
-            CK(launch_frame_gather(h->stream, fb, h->bytes_stride, fnb, S, F, d_bytes, d_bytes ? bytes_cap : 0, d_nb, h->d_err));
-            h->prof.end();
-            h->launches += 1;
-        }
-        if (d_nt) CK(cudaMemsetAsync(d_nt, 0, (size_t)S * sizeof(int), h->stream));
-    }
+    s = rx_device(h, sg, in_kind, d_in, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
+    if (s != DTL_OK) return s;
     return sg.finish();
 }
 
