@@ -39,7 +39,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_BITS, SL_COUNT
+    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_COUNT
 };
 
 } // namespace
@@ -66,7 +66,7 @@ struct dtl_b200 {
     const float2* d_sync1 = nullptr; const float2* d_sync2 = nullptr;
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
-    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0;
+    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16;
     // per-stream state
     int n_streams = 0;
     DevBuf st_buf, carry_buf, pend_buf;
@@ -335,6 +335,11 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
         h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, code.edges));
+        h->screen_bytes = std::max(h->screen_bytes, code.n * 4 + ((code.n + 15) & ~15));
+        if (i + 1 < DTL_MAX_SMEM_CODES) {
+            const int need = 2 * ((code.m + 1) + code.edges + (code.n + 1) + code.edges + code.n);
+            if (h->tab_bytes + ((need + 15) & ~15) <= 64 * 1024) h->tab_bytes += (need + 15) & ~15;
+        }
         h->codes.push_back(std::move(code));
     }
     h->d_codes = h->upload(cd, e);
@@ -611,6 +616,9 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     p.cw_cap = (int)std::min<size_t>(budget * h->max_ncws, 0x7fffffff);
     p.cw_tb = sg.scratch<int>(SL_CWTB, (size_t)p.cw_cap);
     p.cw_nit = sg.scratch<int>(SL_CWNIT, (size_t)p.cw_cap);
+    p.cw_geo = sg.scratch<int>(SL_CWGEO, (size_t)p.cw_cap * 3);
+    p.bp_list = sg.scratch<int>(SL_BPLIST, (size_t)p.cw_cap);
+    p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes;
     p.bits_cap = (long long)budget * ((long long)h->max_ncws * h->max_k + 4);
     p.bits = sg.scratch<uint8_t>(SL_BITS, (size_t)p.bits_cap + 64);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");

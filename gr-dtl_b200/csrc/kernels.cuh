@@ -4,6 +4,8 @@
 
 namespace dtl {
 
+#define DTL_MAX_SMEM_CODES 5     // codes 1..4 get their graph tables staged in shared memory
+
 __host__ __device__ inline int log2n_of(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
 
 // ---- stage 5 ------------------------------------------------------------------------------------------
@@ -56,10 +58,13 @@ struct FecParams {
     int* tb_count;                                 // [S]
     int* tb_list;                                  // compact list of released TB indices
     int* cw_tb; int cw_cap;                        // codeword work list: TB index of work item
-    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs
+    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs, [3] queued for BP
     unsigned long long* bits_used;                 // bump allocator of the bit scratch
     uint8_t* bits; long long bits_cap;             // decoded TB bits, one byte per bit, then packed in place
     int* cw_nit;                                   // [cw_cap]
+    int* cw_geo;                                   // [cw_cap][3]: first LLR of the codeword in the TB, first data bit, k_
+    int* bp_list;                                  // [cw_cap] codewords that failed the initial syndrome check (cnt[3] of them)
+    int tab_bytes, screen_bytes;                   // shared-memory graph tables; per-warp bytes of the screening pass
     int max_it; double sigma2; int mode; int warp_bytes;
     // outputs
     uint8_t* bytes; int bytes_cap; int* nbytes; dtl_tb_result* tb_out; int tb_cap; int* ntbs;

@@ -71,7 +71,14 @@ __global__ void tb_plan_kernel(FecParams p)
         d.stream = s; d.fec_id = fec_id; d.ncws = ncws; d.payload_len = payload_len; d.tb_no = tb_no;
         d.frame_index = frame_index; d.nseg = rcv.nseg; d.cw_first = first; d.bit_base = bit_base;
         for (int i = 0; i < rcv.nseg; i++) d.seg[i] = rcv.seg[i];
-        for (int i = 0; i < ncws; i++) p.cw_tb[first + i] = gi;
+        int rem = payload_len, rcv_idx = 0, d_idx = 0;                   // codeword geometry (tb_decoder.cc:161-183)
+        for (int i = 0; i < ncws; i++) {
+            int k_ = rem / (ncws - i);
+            if (rem % (ncws - i)) ++k_;
+            p.cw_tb[first + i] = gi;
+            p.cw_geo[3 * (first + i)] = rcv_idx; p.cw_geo[3 * (first + i) + 1] = d_idx; p.cw_geo[3 * (first + i) + 2] = k_;
+            rem -= k_; rcv_idx += (c.n - c.k) + k_; d_idx += k_;
+        }
         p.tb_list[atomicAdd(&p.cnt[2], 1)] = gi;
         ntb++;
     };
@@ -154,13 +161,30 @@ __device__ __forceinline__ float rcv_at(const TbDesc& d, int idx, const FecParam
 
 // ---- awgn_bp::decode for one codeword per warp ---------------------------------------------------------------
 // Shared memory per warp: msg[edges] double (Q and R share storage: a check overwrites its Q's with R's, a
-// variable overwrites its R's with Q's), lr0[n] double (channel likelihood ratios), rx[n] float, est[n] u8.
+// variable overwrites its R's with Q's), lr0[n] double (channel likelihood ratios), est[n] u8.  The received
+// values rx[n] (float) are only needed until lr0 is built and live at the start of the msg area.
 struct WarpBuf { double* msg; double* lr0; float* rx; uint8_t* est; };
 
 size_t ldpc_warp_bytes(int n, int edges)
 {
-    size_t b = (size_t)edges * 8 + (size_t)n * 8 + (size_t)n * 4 + (size_t)((n + 15) & ~15);
+    size_t msg = (size_t)edges * 8;
+    if (msg < (size_t)n * 4) msg = (size_t)n * 4;
+    msg = (msg + 7) & ~(size_t)7;
+    size_t b = msg + (size_t)n * 8 + (size_t)((n + 15) & ~15);
     return (b + 15) & ~(size_t)15;
+}
+
+__device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int edges)
+{
+    size_t msg = (size_t)edges * 8;
+    if (msg < (size_t)n * 4) msg = (size_t)n * 4;
+    msg = (msg + 7) & ~(size_t)7;
+    WarpBuf w;
+    w.msg = (double*)base;
+    w.rx = (float*)base;
+    w.lr0 = (double*)(base + msg);
+    w.est = (uint8_t*)(base + msg + (size_t)n * 8);
+    return w;
 }
 
 __device__ __forceinline__ bool syndrome_nonzero(const CodeDev& c, const uint8_t* est, int lane)
@@ -174,58 +198,115 @@ __device__ __forceinline__ bool syndrome_nonzero(const CodeDev& c, const uint8_t
     return __any_sync(0xffffffffu, bad);
 }
 
-// rx[] (H column order, rx < 0 => bit 1) must be filled; returns the iteration count, est[] = decisions.
-__device__ int bp_reference(const CodeDev& c, const WarpBuf& w, int lane, int max_it, double sigma2)
+// One flooding iteration, generic degrees (awgn_bp::update_chks / update_vars, products in alist order).
+__device__ __noinline__ void bp_iter_generic(const CodeDev& c, const WarpBuf& w, int lane)
 {
-    for (int v = lane; v < c.n; v += 32) w.est[v] = w.rx[v] < 0.f ? 1 : 0;          // compute_init_estimate
+    for (int r = lane; r < c.m; r += 32) {                                         // update_chks
+        const int e0 = c.row_ptr[r], e1 = c.row_ptr[r + 1];
+        double prod = 1.0;
+        for (int e = e0; e < e1; e++)
+            prod = __dmul_rn(prod, __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0));
+        for (int e = e0; e < e1; e++) {
+            const double t = __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0);
+            const double pp = __ddiv_rn(prod, t);
+            w.msg[e] = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
+        }
+    }
     __syncwarp();
-    if (!syndrome_nonzero(c, w.est, lane)) return 0;
-    for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc + spa_initialize
+    for (int v = lane; v < c.n; v += 32) {                                         // update_vars + decision
+        const int q0 = c.col_ptr[v], q1 = c.col_ptr[v + 1];
+        double sacc = w.lr0[v];
+        for (int q = q0; q < q1; q++) sacc = __dmul_rn(sacc, w.msg[c.col_edge[q]]);
+        for (int q = q0; q < q1; q++) { const int e = c.col_edge[q]; w.msg[e] = __ddiv_rn(sacc, w.msg[e]); }
+        w.est[v] = sacc > 1.0 ? 1 : 0;
+    }
+    __syncwarp();
+}
+
+// The same iteration for row weight <= RMAX and column weight <= CMAX with the per-edge work unrolled and
+// predicated: the RMAX (CMAX) double-precision divisions of a row (column) are independent instruction chains the
+// scheduler can interleave, and each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
+template <int RMAX, int CMAX>
+__device__ __noinline__ void bp_iter_unrolled(const CodeDev& c, const WarpBuf& w, int lane)
+{
+    for (int r = lane; r < c.m; r += 32) {
+        const int e0 = c.row_ptr[r], deg = c.row_ptr[r + 1] - e0;
+        double t[RMAX];
+#pragma unroll
+        for (int j = 0; j < RMAX; j++)
+            t[j] = j < deg ? __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e0 + j])), 1.0) : 1.0;
+        double prod = 1.0;
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) if (j < deg) prod = __dmul_rn(prod, t[j]);
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) {
+            const double pp = __ddiv_rn(prod, t[j]);
+            const double o = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
+            if (j < deg) w.msg[e0 + j] = o;
+        }
+    }
+    __syncwarp();
+    for (int v = lane; v < c.n; v += 32) {
+        const int q0 = c.col_ptr[v], deg = c.col_ptr[v + 1] - q0;
+        int e[CMAX]; double mv[CMAX];
+#pragma unroll
+        for (int j = 0; j < CMAX; j++) { e[j] = j < deg ? c.col_edge[q0 + j] : 0; mv[j] = j < deg ? w.msg[e[j]] : 1.0; }
+        double sacc = w.lr0[v];
+#pragma unroll
+        for (int j = 0; j < CMAX; j++) if (j < deg) sacc = __dmul_rn(sacc, mv[j]);
+#pragma unroll
+        for (int j = 0; j < CMAX; j++) { const double o = __ddiv_rn(sacc, mv[j]); if (j < deg) w.msg[e[j]] = o; }
+        w.est[v] = sacc > 1.0 ? 1 : 0;
+    }
+    __syncwarp();
+}
+
+// rx[] (H column order, rx < 0 => bit 1) and est[] (hard decisions of rx, known to fail the syndrome check) must be
+// filled; returns the iteration count, est[] = final decisions.
+__device__ int bp_reference_run(const CodeDev& c, const WarpBuf& w, int lane, int max_it, double sigma2)
+{
+    for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc
         const float m2 = -1 * 2 * w.rx[v];
-        const double lr = exp(__ddiv_rn((double)m2, sigma2));
-        w.lr0[v] = lr;
+        w.lr0[v] = exp(__ddiv_rn((double)m2, sigma2));
+    }
+    __syncwarp();                                                                      // rx (aliases msg) is dead now
+    for (int v = lane; v < c.n; v += 32) {                                             // spa_initialize
+        const double lr = w.lr0[v];
         for (int q = c.col_ptr[v]; q < c.col_ptr[v + 1]; q++) w.msg[c.col_edge[q]] = lr;
     }
     __syncwarp();
+    // pick the unrolled instance that matches the code's degrees exactly (no wasted divisions)
+    int kind = 0;
+    if (c.max_col <= 4 && c.max_row <= 8) kind = (c.max_row <= 4 ? 1 : c.max_row == 5 ? 2 : c.max_row == 6 ? 3 : 4) + (c.max_col <= 3 ? 0 : 4);
     int nit = 0;
     while (nit < max_it) {
         nit++;
-        for (int r = lane; r < c.m; r += 32) {                                         // update_chks
-            const int e0 = c.row_ptr[r], e1 = c.row_ptr[r + 1];
-            double prod = 1.0;
-            for (int e = e0; e < e1; e++)
-                prod = __dmul_rn(prod, __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0));
-            for (int e = e0; e < e1; e++) {
-                const double t = __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0);
-                const double pp = __ddiv_rn(prod, t);
-                w.msg[e] = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
-            }
+        switch (kind) {
+        case 1: bp_iter_unrolled<4, 3>(c, w, lane); break;
+        case 2: bp_iter_unrolled<5, 3>(c, w, lane); break;
+        case 3: bp_iter_unrolled<6, 3>(c, w, lane); break;
+        case 4: bp_iter_unrolled<8, 3>(c, w, lane); break;
+        case 5: bp_iter_unrolled<4, 4>(c, w, lane); break;
+        case 6: bp_iter_unrolled<5, 4>(c, w, lane); break;
+        case 7: bp_iter_unrolled<6, 4>(c, w, lane); break;
+        case 8: bp_iter_unrolled<8, 4>(c, w, lane); break;
+        default: bp_iter_generic(c, w, lane); break;
         }
-        __syncwarp();
-        for (int v = lane; v < c.n; v += 32) {                                         // update_vars + decision
-            const int q0 = c.col_ptr[v], q1 = c.col_ptr[v + 1];
-            double sacc = w.lr0[v];
-            for (int q = q0; q < q1; q++) sacc = __dmul_rn(sacc, w.msg[c.col_edge[q]]);
-            for (int q = q0; q < q1; q++) { const int e = c.col_edge[q]; w.msg[e] = __ddiv_rn(sacc, w.msg[e]); }
-            w.est[v] = sacc > 1.0 ? 1 : 0;
-        }
-        __syncwarp();
         if (!syndrome_nonzero(c, w.est, lane)) break;
     }
     return nit;
 }
 
-// Layered normalised min-sum (fp32, LLR domain, rx > 0 => bit 0): check rows are processed in order,
-// each lane owning whole rows of a 32-row layer group is not conflict-free for arbitrary alists, so rows are
-// processed one at a time by the lanes of the warp cooperating over the row's edges (row weight <= 32).
-__device__ int bp_layered(const CodeDev& c, const WarpBuf& w, int lane, int max_it)
+// Layered normalised min-sum (fp32, LLR domain, rx > 0 => bit 0): check rows are processed in order, the lanes of
+// the warp cooperating over one row's edges (row weight <= 32).  est[] must hold the hard decisions of rx.
+__device__ int bp_layered_run(const CodeDev& c, const WarpBuf& w, int lane, int max_it)
 {
     float* post = (float*)w.lr0;                  // posterior LLR per variable
     float* cmsg = (float*)w.msg;                  // check->variable message per edge
-    for (int v = lane; v < c.n; v += 32) { post[v] = w.rx[v]; w.est[v] = w.rx[v] < 0.f ? 1 : 0; }
+    for (int v = lane; v < c.n; v += 32) post[v] = w.rx[v];
+    __syncwarp();                                 // rx (aliases cmsg) is dead now
     for (int e = lane; e < c.edges; e += 32) cmsg[e] = 0.f;
     __syncwarp();
-    if (!syndrome_nonzero(c, w.est, lane)) return 0;
     const float norm = 0.8125f;
     int nit = 0;
     while (nit < max_it) {
@@ -261,47 +342,109 @@ __device__ int bp_layered(const CodeDev& c, const WarpBuf& w, int lane, int max_
     return nit;
 }
 
-__device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int edges)
+// Copies the codes' graph tables into shared memory and returns CodeDev records whose pointers point there
+// (generic addressing).  tab = 2-byte aligned area of `tab_bytes`; falls back to the global tables when they do not fit.
+__device__ void stage_codes(const FecParams& p, CodeDev* scodes, unsigned char* tab)
 {
-    WarpBuf w;
-    w.msg = (double*)base;
-    w.lr0 = (double*)(base + (size_t)edges * 8);
-    w.rx = (float*)(base + (size_t)edges * 8 + (size_t)n * 8);
-    w.est = (uint8_t*)(base + (size_t)edges * 8 + (size_t)n * 8 + (size_t)n * 4);
-    return w;
+    const int nthr = blockDim.x;
+    size_t off = 0;
+    for (int ci = 1; ci <= p.n_codes && ci < DTL_MAX_SMEM_CODES; ci++) {
+        const CodeDev g = p.codes[ci];
+        const size_t need = 2 * ((size_t)(g.m + 1) + g.edges + (g.n + 1) + g.edges + g.n);
+        CodeDev sc = g;
+        if (off + need <= (size_t)p.tab_bytes) {
+            uint16_t* d = (uint16_t*)(tab + off);
+            uint16_t* row_ptr = d; d += g.m + 1;
+            uint16_t* row_var = d; d += g.edges;
+            uint16_t* col_ptr = d; d += g.n + 1;
+            uint16_t* col_edge = d; d += g.edges;
+            uint16_t* permute = d;
+            for (int i = threadIdx.x; i <= g.m; i += nthr) row_ptr[i] = g.row_ptr[i];
+            for (int i = threadIdx.x; i < g.edges; i += nthr) { row_var[i] = g.row_var[i]; col_edge[i] = g.col_edge[i]; }
+            for (int i = threadIdx.x; i <= g.n; i += nthr) col_ptr[i] = g.col_ptr[i];
+            for (int i = threadIdx.x; i < g.n; i += nthr) permute[i] = g.permute[i];
+            sc.row_ptr = row_ptr; sc.row_var = row_var; sc.col_ptr = col_ptr; sc.col_edge = col_edge; sc.permute = permute;
+            off += (need + 15) & ~(size_t)15;
+        }
+        if (threadIdx.x == 0) scodes[ci] = sc;
+    }
+    __syncthreads();
 }
 
-__global__ void __launch_bounds__(256) ldpc_tb_kernel(FecParams p)
+__device__ __forceinline__ const CodeDev& code_of(const FecParams& p, const CodeDev* scodes, int fec_id)
+{
+    return fec_id < DTL_MAX_SMEM_CODES ? scodes[fec_id] : p.codes[fec_id];
+}
+
+// Gather of one codeword: n LLRs of the TB's receive buffer (shortened positions = -15, tb_decoder.cc:145,161-183),
+// negated and permuted into H column order (ldpc_dec.cc:64-66), plus the hard decisions (compute_init_estimate).
+__device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, const CodeDev& c, int it, float* rx, uint8_t* est, int lane)
+{
+    const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], ncheck = c.n - c.k;
+    for (int q = lane; q < c.n; q += 32) {
+        const float v = q < ncheck + k_ ? rcv_at(d, rcv_idx + q, p) : -15.0f;
+        const float x = -1 * v;
+        const int col = c.permute[q];
+        rx[col] = x;
+        est[col] = x < 0.f ? 1 : 0;
+    }
+    __syncwarp();
+}
+
+// Pass 1, one warp per codeword, tiny footprint (full occupancy, HBM-latency hidden): gather, hard decision, syndrome.
+// A zero syndrome is awgn_bp's exit before the first iteration (nit = 0): the systematic bits go out right away;
+// anything else is queued for the belief-propagation pass.
+__global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    unsigned char* base = sm + (size_t)wid * p.warp_bytes;
+    __shared__ CodeDev scodes[DTL_MAX_SMEM_CODES];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    stage_codes(p, scodes, sm);
     const int total = min(p.cnt[0], p.cw_cap);
-    for (;;) {
-        int it = 0;
-        if (lane == 0) it = atomicAdd(&p.cnt[1], 1);
-        it = __shfl_sync(0xffffffffu, it, 0);
-        if (it >= total) break;
+    unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.screen_bytes;
+    for (int it = blockIdx.x * warps + wid; it < total; it += gridDim.x * warps) {
         const TbDesc& d = p.tbs[p.cw_tb[it]];
-        const CodeDev& c = p.codes[d.fec_id];
-        const int ci = it - d.cw_first, ncheck = c.n - c.k;
-        // codeword geometry inside the TB (tb_decoder.cc:161-183)
-        int rem = d.payload_len, rcv_idx = 0, d_idx = 0, k_ = 0;
-        for (int i = 0; i <= ci; i++) {
-            k_ = rem / (d.ncws - i);
-            if (rem % (d.ncws - i)) ++k_;
-            if (i < ci) { rem -= k_; rcv_idx += ncheck + k_; d_idx += k_; }
-        }
-        const WarpBuf w = carve(base, c.n, c.edges);
-        for (int q = lane; q < c.n; q += 32) {                              // ldpc_dec.cc:64-66
-            const float v = q < ncheck + k_ ? rcv_at(d, rcv_idx + q, p) : -15.0f;
-            w.rx[c.permute[q]] = -1 * v;
+        const CodeDev& c = code_of(p, scodes, d.fec_id);
+        float* rx = (float*)base;
+        uint8_t* est = base + (size_t)c.n * 4;
+        gather_cw(p, d, c, it, rx, est, lane);
+        const bool bad = syndrome_nonzero(c, est, lane);
+        if (!bad) {
+            const int d_idx = p.cw_geo[3 * it + 1], k_ = p.cw_geo[3 * it + 2];
+            uint8_t* out = p.bits + d.bit_base + d_idx;
+            for (int q = lane; q < k_; q += 32) out[q] = est[c.permute[c.rank + q]];   // cldpc::get_systematic_bits
+            if (lane == 0) p.cw_nit[it] = 0;
+        } else if (lane == 0) {
+            p.bp_list[atomicAdd(&p.cnt[3], 1)] = it;
         }
         __syncwarp();
-        const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered(c, w, lane, p.max_it)
-                                                   : bp_reference(c, w, lane, p.max_it, p.sigma2);
+    }
+}
+
+// Pass 2, persistent: each warp pulls queued codewords from a device counter and runs the decoder proper.
+__global__ void __launch_bounds__(128, 4) ldpc_bp_kernel(FecParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ CodeDev scodes[DTL_MAX_SMEM_CODES];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    stage_codes(p, scodes, sm);
+    unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.warp_bytes;
+    const int total = p.cnt[3];
+    for (;;) {
+        int j = 0;
+        if (lane == 0) j = atomicAdd(&p.cnt[1], 1);
+        j = __shfl_sync(0xffffffffu, j, 0);
+        if (j >= total) break;
+        const int it = p.bp_list[j];
+        const TbDesc& d = p.tbs[p.cw_tb[it]];
+        const CodeDev& c = code_of(p, scodes, d.fec_id);
+        const WarpBuf w = carve(base, c.n, c.edges);
+        gather_cw(p, d, c, it, w.rx, w.est, lane);
+        const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered_run(c, w, lane, p.max_it)
+                                                   : bp_reference_run(c, w, lane, p.max_it, p.sigma2);
+        const int d_idx = p.cw_geo[3 * it + 1], k_ = p.cw_geo[3 * it + 2];
         uint8_t* out = p.bits + d.bit_base + d_idx;
-        for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute[c.rank + q]];   // cldpc::get_systematic_bits
+        for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute[c.rank + q]];
         if (lane == 0) p.cw_nit[it] = nit;
         __syncwarp();
     }
@@ -319,17 +462,21 @@ __global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
         it = __shfl_sync(0xffffffffu, it, 0);
         if (it >= p.count) break;
         const float* in = p.llr + it * c.n;
-        for (int q = lane; q < c.n; q += 32) w.rx[c.permute[q]] = -1 * in[q];
+        for (int q = lane; q < c.n; q += 32) {                                      // ldpc_dec.cc:64-66
+            const float x = -1 * in[q];
+            const int col = c.permute[q];
+            w.rx[col] = x; w.est[col] = x < 0.f ? 1 : 0;
+        }
         __syncwarp();
-        const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered(c, w, lane, p.max_it)
-                                                   : bp_reference(c, w, lane, p.max_it, p.sigma2);
+        int nit = 0;
+        if (syndrome_nonzero(c, w.est, lane))
+            nit = p.mode == DTL_LDPC_LAYERED ? bp_layered_run(c, w, lane, p.max_it) : bp_reference_run(c, w, lane, p.max_it, p.sigma2);
         uint8_t* out = p.bits + it * c.k;
         for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute[c.rank + q]];
         if (lane == 0 && p.nit) p.nit[it] = nit;
         __syncwarp();
     }
 }
-
 
 // ---- TB epilogue: bits -> bytes LSB-first, CRC-32 verify (fec_decoder_impl.cc:161-204) -------------------------
 // One warp per released TB.  The TB's bits (one per byte) are packed in place: the 32 bits of word w are
@@ -425,7 +572,7 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
     }
 }
 
-__global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = 0; *bits_used = 0ull; }
+__global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; *bits_used = 0ull; }
 
 cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof)
 {
@@ -435,27 +582,38 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
     tb_plan_kernel<<<(p.n_streams + 127) / 128, 128, 0, st>>>(p);
     prof->end();
-    const int warps = 8;
-    const size_t smem = (size_t)p.warp_bytes * warps;
-    if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-    static size_t attr_set = 0;
-    if (smem > 48 * 1024 && smem > attr_set) {
-        cudaFuncSetAttribute(ldpc_tb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = smem;
+    {   // pass 1: screening, grid-stride over the codeword work list
+        const size_t smem = (size_t)p.tab_bytes + 8 * (size_t)p.screen_bytes;
+        static size_t attr_set = 0;
+        if (smem > 48 * 1024 && smem > attr_set) {
+            cudaFuncSetAttribute(ldpc_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            attr_set = smem;
+        }
+        prof->begin(DTL_STAGE_LDPC, 2);
+        ldpc_screen_kernel<<<sm_count * 8, 256, smem, st>>>(p);
     }
-    int per_sm = (int)((220 * 1024) / (smem + 1024));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm > 8) per_sm = 8;
-    prof->begin(DTL_STAGE_LDPC, 1);
-    ldpc_tb_kernel<<<sm_count * per_sm, warps * 32, smem, st>>>(p);
-    prof->end();
+    {   // pass 2: belief propagation on what did not pass, persistent
+        const int warps = 4;
+        const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
+        if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+        static size_t attr_set = 0;
+        if (smem > 48 * 1024 && smem > attr_set) {
+            cudaFuncSetAttribute(ldpc_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            attr_set = smem;
+        }
+        int per_sm = (int)((226 * 1024) / (smem + 1024));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > 8) per_sm = 8;
+        ldpc_bp_kernel<<<sm_count * per_sm, warps * 32, smem, st>>>(p);
+        prof->end();
+    }
     const int tb_max = p.n_streams * p.tb_slots;
     prof->begin(DTL_STAGE_TBFINISH, 3);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
     tb_gather_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     prof->end();
-    if (launches) *launches += 6;
+    if (launches) *launches += 7;
     return cudaGetLastError();
 }
 
