@@ -310,14 +310,20 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
     for (int i = 0; i < c->n_codes; i++) {
         Code code; std::string err;
         if (!load_alist(c->alist_paths[i], code, err)) return fail(h, DTL_ERR_IO, err);
-        std::vector<uint16_t> row_ptr(code.m + 1, 0), row_var, col_ptr(code.n + 1, 0), col_edge, perm(code.n);
-        for (int r = 0; r < code.m; r++) { for (int v : code.mlist[r]) row_var.push_back((uint16_t)v); row_ptr[r + 1] = (uint16_t)row_var.size(); }
+        // slot-major edge storage: edge j of row r (mlist order) is slot j*m + r (kernels_fec.cu)
+        const int slots = code.max_row * code.m;
+        if (slots > 65535) return fail(h, DTL_ERR_UNSUPPORTED, "LDPC graph too large (max_row * m > 65535)");
+        std::vector<uint16_t> row_len(code.m, 0), row_var((size_t)slots, 0), col_ptr(code.n + 1, 0), col_edge, perm(code.n);
+        for (int r = 0; r < code.m; r++) {
+            row_len[r] = (uint16_t)code.mlist[r].size();
+            for (size_t j = 0; j < code.mlist[r].size(); j++) row_var[j * code.m + r] = (uint16_t)code.mlist[r][j];
+        }
         for (int v = 0; v < code.n; v++) {
             for (int r : code.nlist[v]) {
                 int pos = -1;
                 for (size_t q = 0; q < code.mlist[r].size(); q++) if (code.mlist[r][q] == v) pos = (int)q;
                 if (pos < 0) return fail(h, DTL_ERR_IO, "alist row/column lists disagree in " + code.path);
-                col_edge.push_back((uint16_t)(row_ptr[r] + pos));
+                col_edge.push_back((uint16_t)(pos * code.m + r));
             }
             col_ptr[v + 1] = (uint16_t)col_edge.size();
         }
@@ -329,17 +335,16 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         if (code.max_row > 32) return fail(h, DTL_ERR_UNSUPPORTED, "LDPC row weight > 32");
         CodeDev& d = code.dev;
         d.n = code.n; d.m = code.m; d.k = code.k; d.rank = code.rank; d.edges = code.edges; d.max_row = code.max_row; d.max_col = code.max_col;
-        d.row_ptr = h->upload(row_ptr, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
+        d.row_len = h->upload(row_len, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
         d.col_edge = h->upload(col_edge, e); d.permute = h->upload(perm, e);
         d.pmat = h->upload(pmat, e); d.kwords = kwords;
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
-        h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, code.edges));
+        h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, slots));
         h->screen_bytes = std::max(h->screen_bytes, code.n * 4 + ((code.n + 15) & ~15));
-        if (i + 1 < DTL_MAX_SMEM_CODES) {
-            const int need = 2 * ((code.m + 1) + code.edges + (code.n + 1) + code.edges + code.n);
-            if (h->tab_bytes + ((need + 15) & ~15) <= 64 * 1024) h->tab_bytes += (need + 15) & ~15;
-        }
+        h->tab_bytes += (int)ldpc_tab_bytes(code.n, code.m, slots, code.edges);
+        if (i + 1 >= DTL_MAX_SMEM_CODES || h->tab_bytes > 96 * 1024)
+            return fail(h, DTL_ERR_UNSUPPORTED, "too many / too large LDPC codes for the shared-memory graph tables");
         h->codes.push_back(std::move(code));
     }
     h->d_codes = h->upload(cd, e);
@@ -782,7 +787,8 @@ extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const fl
     LdpcParams p;
     memset(&p, 0, sizeof p);
     p.code = c.dev; p.count = count; p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode;
-    p.cursor = h->d_cursor; p.warp_bytes = h->warp_bytes;
+    p.cursor = h->d_cursor; p.warp_bytes = (int)ldpc_warp_bytes(c.n, c.max_row * c.m);
+    p.tab_bytes = (int)ldpc_tab_bytes(c.n, c.m, c.max_row * c.m, c.edges);
     p.llr = sg.in(SL_LLR, llr, (size_t)count * c.n);
     p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
     p.nit = sg.out(SL_NIT, nit, (size_t)count);

@@ -43,10 +43,10 @@ struct PlanDev {
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.
 struct CodeDev {
     int n, m, k, rank, edges, max_row, max_col;
-    const uint16_t* row_ptr;     // [m+1] edges are stored check-major (mlist order)
-    const uint16_t* row_var;     // [edges] variable of edge
+    const uint16_t* row_len;     // [m] row weight; edge j of row r (mlist order) lives in slot j*m + r
+    const uint16_t* row_var;     // [max_row*m] variable of slot
     const uint16_t* col_ptr;     // [n+1]
-    const uint16_t* col_edge;    // [edges] edge ids of variable v in nlist order
+    const uint16_t* col_edge;    // [edges] slots of variable v's edges in nlist order
     const uint16_t* permute;     // [n]
     const uint32_t* pmat;        // [rank][kwords] parity part of the systematic generator, bit j of row i = P[i][j]
     int kwords;                  // ceil(k / 32)

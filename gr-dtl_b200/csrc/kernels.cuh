@@ -73,7 +73,7 @@ struct FecParams {
 
 struct LdpcParams {                                // stand-alone fec_dec::decode batches
     CodeDev code; const float* llr; long long count; uint8_t* bits; int* nit; int max_it; double sigma2; int mode;
-    int* cursor; int warp_bytes;
+    int* cursor; int warp_bytes; int tab_bytes;
 };
 
 struct DemapParams {
@@ -89,7 +89,8 @@ cudaError_t launch_eq(cudaStream_t st, const EqParams& p);
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
 cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof);
-size_t ldpc_warp_bytes(int n, int edges);
+size_t ldpc_warp_bytes(int n, int slots);
+size_t ldpc_tab_bytes(int n, int m, int slots, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
 cudaError_t launch_ldpc_encode(cudaStream_t st, const CodeDev& code, const uint8_t* data, long long count, uint8_t* wire);
 cudaError_t launch_demap(cudaStream_t st, const DemapParams& p);   // mode 0 soft, 1 hard, 2 map

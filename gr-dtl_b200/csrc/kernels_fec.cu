@@ -143,42 +143,46 @@ __global__ void tb_plan_kernel(FecParams p)
     if (err) atomicOr(p.err, err);
 }
 
-// LLR number `idx` of a TB's receive buffer; reads past the received length return 0 (erasure).
-__device__ __forceinline__ float rcv_at(const TbDesc& d, int idx, const FecParams& p)
-{
-    int base = 0;
-    for (int i = 0; i < d.nseg; i++) {
-        const TbSeg sg = d.seg[i];
-        if (idx < base + sg.len) {
-            const int o = sg.start + (idx - base);
-            if (sg.src < 0) return p.carry[(size_t)d.stream * p.carry_cap + o];
-            return __ldcs(&p.llr[((size_t)d.stream * p.F + sg.src) * p.llr_stride + o]);
-        }
-        base += sg.len;
-    }
-    return 0.0f;
-}
-
 // ---- awgn_bp::decode for one codeword per warp ---------------------------------------------------------------
-// Shared memory per warp: msg[edges] double (Q and R share storage: a check overwrites its Q's with R's, a
-// variable overwrites its R's with Q's), lr0[n] double (channel likelihood ratios), est[n] u8.  The received
-// values rx[n] (float) are only needed until lr0 is built and live at the start of the msg area.
+// Graph tables live in shared memory (staged once per CTA).  Edge storage is slot-major: edge j of check row r
+// (alist order) is slot j*m + r, so the lanes of a warp, which own consecutive rows, touch consecutive doubles
+// (no bank conflicts in the check pass); col_edge[] lists the slots of a variable's edges in alist order.
+// Per warp: msg[slots] double (Q and R share storage: a check overwrites its Q's with R's, a variable its R's
+// with Q's), lr0[n] double (channel likelihood ratios), est[n] u8.  The received values rx[n] (float) are only
+// needed until lr0 is built and live at the start of the msg area.
+struct CodeS {
+    int n, m, k, rank, slots, max_row, max_col;
+    int o_row_len, o_row_var, o_col_ptr, o_col_edge, o_permute;     // byte offsets from the CTA's dynamic shared memory
+    const unsigned char* smb;                                       // = the kernel's `sm` (set in the kernel body so the
+                                                                    //   compiler keeps the accesses in the shared space)
+    __device__ __forceinline__ const uint16_t* row_len() const { return (const uint16_t*)(smb + o_row_len); }
+    __device__ __forceinline__ const uint16_t* row_var() const { return (const uint16_t*)(smb + o_row_var); }
+    __device__ __forceinline__ const uint16_t* col_ptr() const { return (const uint16_t*)(smb + o_col_ptr); }
+    __device__ __forceinline__ const uint16_t* col_edge() const { return (const uint16_t*)(smb + o_col_edge); }
+    __device__ __forceinline__ const uint16_t* permute() const { return (const uint16_t*)(smb + o_permute); }
+};
 struct WarpBuf { double* msg; double* lr0; float* rx; uint8_t* est; };
 
-size_t ldpc_warp_bytes(int n, int edges)
+static __host__ __device__ inline size_t code_tab_bytes(int n, int m, int slots, int edges)
 {
-    size_t msg = (size_t)edges * 8;
+    return (2 * ((size_t)m + slots + (n + 1) + edges + n) + 15) & ~(size_t)15;
+}
+size_t ldpc_tab_bytes(int n, int m, int slots, int edges) { return code_tab_bytes(n, m, slots, edges); }
+
+static __host__ __device__ inline size_t warp_msg_bytes(int n, int slots)
+{
+    size_t msg = (size_t)slots * 8;
     if (msg < (size_t)n * 4) msg = (size_t)n * 4;
-    msg = (msg + 7) & ~(size_t)7;
-    size_t b = msg + (size_t)n * 8 + (size_t)((n + 15) & ~15);
-    return (b + 15) & ~(size_t)15;
+    return (msg + 7) & ~(size_t)7;
+}
+size_t ldpc_warp_bytes(int n, int slots)
+{
+    return (warp_msg_bytes(n, slots) + (size_t)n * 8 + (size_t)((n + 15) & ~15) + 15) & ~(size_t)15;
 }
 
-__device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int edges)
+__device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int slots)
 {
-    size_t msg = (size_t)edges * 8;
-    if (msg < (size_t)n * 4) msg = (size_t)n * 4;
-    msg = (msg + 7) & ~(size_t)7;
+    const size_t msg = warp_msg_bytes(n, slots);
     WarpBuf w;
     w.msg = (double*)base;
     w.rx = (float*)base;
@@ -187,54 +191,79 @@ __device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int edges)
     return w;
 }
 
-__device__ __forceinline__ bool syndrome_nonzero(const CodeDev& c, const uint8_t* est, int lane)
+// Copies one code's tables from HBM into shared memory at `tab` (all threads of the CTA) and returns the
+// shared-memory view.  The caller synchronises.
+__device__ __forceinline__ CodeS stage_code(const CodeDev& g, unsigned char* sm, int tab_off)
+{
+    const int nthr = blockDim.x, slots = g.max_row * g.m;
+    uint16_t* d = (uint16_t*)(sm + tab_off);
+    uint16_t* row_len = d; d += g.m;
+    uint16_t* row_var = d; d += slots;
+    uint16_t* col_ptr = d; d += g.n + 1;
+    uint16_t* col_edge = d; d += g.edges;
+    uint16_t* permute = d;
+    for (int i = threadIdx.x; i < g.m; i += nthr) row_len[i] = g.row_len[i];
+    for (int i = threadIdx.x; i < slots; i += nthr) row_var[i] = g.row_var[i];
+    for (int i = threadIdx.x; i <= g.n; i += nthr) col_ptr[i] = g.col_ptr[i];
+    for (int i = threadIdx.x; i < g.edges; i += nthr) col_edge[i] = g.col_edge[i];
+    for (int i = threadIdx.x; i < g.n; i += nthr) permute[i] = g.permute[i];
+    CodeS c;
+    c.n = g.n; c.m = g.m; c.k = g.k; c.rank = g.rank; c.slots = slots; c.max_row = g.max_row; c.max_col = g.max_col;
+    c.o_row_len = tab_off; c.o_row_var = c.o_row_len + 2 * g.m; c.o_col_ptr = c.o_row_var + 2 * slots;
+    c.o_col_edge = c.o_col_ptr + 2 * (g.n + 1); c.o_permute = c.o_col_edge + 2 * g.edges;
+    c.smb = sm;
+    return c;
+}
+
+__device__ __forceinline__ bool syndrome_nonzero(const CodeS& c, const uint8_t* est, int lane)
 {
     bool bad = false;
     for (int r = lane; r < c.m; r += 32) {
+        const int deg = c.row_len()[r];
         unsigned par = 0;
-        for (int e = c.row_ptr[r]; e < c.row_ptr[r + 1]; e++) par ^= est[c.row_var[e]];
+        for (int j = 0; j < deg; j++) par ^= est[c.row_var()[j * c.m + r]];
         bad |= (par & 1u) != 0;
     }
     return __any_sync(0xffffffffu, bad);
 }
 
-// One flooding iteration, generic degrees (awgn_bp::update_chks / update_vars, products in alist order).
-__device__ __noinline__ void bp_iter_generic(const CodeDev& c, const WarpBuf& w, int lane)
+// One flooding iteration, any degrees (awgn_bp::update_chks / update_vars, products in alist order).
+__device__ __forceinline__ void bp_iter_generic(const CodeS& c, const WarpBuf& w, int lane)
 {
     for (int r = lane; r < c.m; r += 32) {                                         // update_chks
-        const int e0 = c.row_ptr[r], e1 = c.row_ptr[r + 1];
+        const int deg = c.row_len()[r];
         double prod = 1.0;
-        for (int e = e0; e < e1; e++)
-            prod = __dmul_rn(prod, __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0));
-        for (int e = e0; e < e1; e++) {
-            const double t = __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e])), 1.0);
+        for (int j = 0; j < deg; j++)
+            prod = __dmul_rn(prod, __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[j * c.m + r])), 1.0));
+        for (int j = 0; j < deg; j++) {
+            const double t = __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[j * c.m + r])), 1.0);
             const double pp = __ddiv_rn(prod, t);
-            w.msg[e] = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
+            w.msg[j * c.m + r] = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
         }
     }
     __syncwarp();
     for (int v = lane; v < c.n; v += 32) {                                         // update_vars + decision
-        const int q0 = c.col_ptr[v], q1 = c.col_ptr[v + 1];
+        const int q0 = c.col_ptr()[v], q1 = c.col_ptr()[v + 1];
         double sacc = w.lr0[v];
-        for (int q = q0; q < q1; q++) sacc = __dmul_rn(sacc, w.msg[c.col_edge[q]]);
-        for (int q = q0; q < q1; q++) { const int e = c.col_edge[q]; w.msg[e] = __ddiv_rn(sacc, w.msg[e]); }
+        for (int q = q0; q < q1; q++) sacc = __dmul_rn(sacc, w.msg[c.col_edge()[q]]);
+        for (int q = q0; q < q1; q++) { const int e = c.col_edge()[q]; w.msg[e] = __ddiv_rn(sacc, w.msg[e]); }
         w.est[v] = sacc > 1.0 ? 1 : 0;
     }
     __syncwarp();
 }
 
 // The same iteration for row weight <= RMAX and column weight <= CMAX with the per-edge work unrolled and
-// predicated: the RMAX (CMAX) double-precision divisions of a row (column) are independent instruction chains the
-// scheduler can interleave, and each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
+// predicated: the divisions of a row (column) are independent instruction chains the scheduler can interleave,
+// and each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
 template <int RMAX, int CMAX>
-__device__ __noinline__ void bp_iter_unrolled(const CodeDev& c, const WarpBuf& w, int lane)
+__device__ __forceinline__ void bp_iter_unrolled(const CodeS& c, const WarpBuf& w, int lane)
 {
     for (int r = lane; r < c.m; r += 32) {
-        const int e0 = c.row_ptr[r], deg = c.row_ptr[r + 1] - e0;
+        const int deg = c.row_len()[r];
         double t[RMAX];
 #pragma unroll
         for (int j = 0; j < RMAX; j++)
-            t[j] = j < deg ? __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[e0 + j])), 1.0) : 1.0;
+            t[j] = j < deg ? __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[j * c.m + r])), 1.0) : 1.0;
         double prod = 1.0;
 #pragma unroll
         for (int j = 0; j < RMAX; j++) if (j < deg) prod = __dmul_rn(prod, t[j]);
@@ -242,15 +271,15 @@ __device__ __noinline__ void bp_iter_unrolled(const CodeDev& c, const WarpBuf& w
         for (int j = 0; j < RMAX; j++) {
             const double pp = __ddiv_rn(prod, t[j]);
             const double o = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
-            if (j < deg) w.msg[e0 + j] = o;
+            if (j < deg) w.msg[j * c.m + r] = o;
         }
     }
     __syncwarp();
     for (int v = lane; v < c.n; v += 32) {
-        const int q0 = c.col_ptr[v], deg = c.col_ptr[v + 1] - q0;
+        const int q0 = c.col_ptr()[v], deg = c.col_ptr()[v + 1] - q0;
         int e[CMAX]; double mv[CMAX];
 #pragma unroll
-        for (int j = 0; j < CMAX; j++) { e[j] = j < deg ? c.col_edge[q0 + j] : 0; mv[j] = j < deg ? w.msg[e[j]] : 1.0; }
+        for (int j = 0; j < CMAX; j++) { e[j] = j < deg ? c.col_edge()[q0 + j] : 0; mv[j] = j < deg ? w.msg[e[j]] : 1.0; }
         double sacc = w.lr0[v];
 #pragma unroll
         for (int j = 0; j < CMAX; j++) if (j < deg) sacc = __dmul_rn(sacc, mv[j]);
@@ -261,9 +290,22 @@ __device__ __noinline__ void bp_iter_unrolled(const CodeDev& c, const WarpBuf& w
     __syncwarp();
 }
 
+template <int RMAX, int CMAX>
+__device__ __forceinline__ int bp_loop(const CodeS& c, const WarpBuf& w, int lane, int max_it)
+{
+    int nit = 0;
+    while (nit < max_it) {
+        nit++;
+        if (RMAX > 0) bp_iter_unrolled<(RMAX > 0 ? RMAX : 1), (CMAX > 0 ? CMAX : 1)>(c, w, lane);
+        else bp_iter_generic(c, w, lane);
+        if (!syndrome_nonzero(c, w.est, lane)) break;
+    }
+    return nit;
+}
+
 // rx[] (H column order, rx < 0 => bit 1) and est[] (hard decisions of rx, known to fail the syndrome check) must be
 // filled; returns the iteration count, est[] = final decisions.
-__device__ int bp_reference_run(const CodeDev& c, const WarpBuf& w, int lane, int max_it, double sigma2)
+__device__ __forceinline__ int bp_reference_run(const CodeS& c, const WarpBuf& w, int lane, int max_it, double sigma2)
 {
     for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc
         const float m2 = -1 * 2 * w.rx[v];
@@ -272,49 +314,39 @@ __device__ int bp_reference_run(const CodeDev& c, const WarpBuf& w, int lane, in
     __syncwarp();                                                                      // rx (aliases msg) is dead now
     for (int v = lane; v < c.n; v += 32) {                                             // spa_initialize
         const double lr = w.lr0[v];
-        for (int q = c.col_ptr[v]; q < c.col_ptr[v + 1]; q++) w.msg[c.col_edge[q]] = lr;
+        for (int q = c.col_ptr()[v]; q < c.col_ptr()[v + 1]; q++) w.msg[c.col_edge()[q]] = lr;
     }
     __syncwarp();
-    // pick the unrolled instance that matches the code's degrees exactly (no wasted divisions)
-    int kind = 0;
-    if (c.max_col <= 4 && c.max_row <= 8) kind = (c.max_row <= 4 ? 1 : c.max_row == 5 ? 2 : c.max_row == 6 ? 3 : 4) + (c.max_col <= 3 ? 0 : 4);
-    int nit = 0;
-    while (nit < max_it) {
-        nit++;
-        switch (kind) {
-        case 1: bp_iter_unrolled<4, 3>(c, w, lane); break;
-        case 2: bp_iter_unrolled<5, 3>(c, w, lane); break;
-        case 3: bp_iter_unrolled<6, 3>(c, w, lane); break;
-        case 4: bp_iter_unrolled<8, 3>(c, w, lane); break;
-        case 5: bp_iter_unrolled<4, 4>(c, w, lane); break;
-        case 6: bp_iter_unrolled<5, 4>(c, w, lane); break;
-        case 7: bp_iter_unrolled<6, 4>(c, w, lane); break;
-        case 8: bp_iter_unrolled<8, 4>(c, w, lane); break;
-        default: bp_iter_generic(c, w, lane); break;
-        }
-        if (!syndrome_nonzero(c, w.est, lane)) break;
+    // the unrolled instance that matches the code's degrees exactly (no wasted divisions)
+    if (c.max_col <= 3) {
+        if (c.max_row <= 4) return bp_loop<4, 3>(c, w, lane, max_it);
+        if (c.max_row <= 6) return bp_loop<6, 3>(c, w, lane, max_it);
+        if (c.max_row <= 8) return bp_loop<8, 3>(c, w, lane, max_it);
+    } else if (c.max_col <= 4) {
+        if (c.max_row <= 5) return bp_loop<5, 4>(c, w, lane, max_it);
+        if (c.max_row <= 8) return bp_loop<8, 4>(c, w, lane, max_it);
     }
-    return nit;
+    return bp_loop<0, 0>(c, w, lane, max_it);
 }
 
 // Layered normalised min-sum (fp32, LLR domain, rx > 0 => bit 0): check rows are processed in order, the lanes of
 // the warp cooperating over one row's edges (row weight <= 32).  est[] must hold the hard decisions of rx.
-__device__ int bp_layered_run(const CodeDev& c, const WarpBuf& w, int lane, int max_it)
+__device__ __forceinline__ int bp_layered_run(const CodeS& c, const WarpBuf& w, int lane, int max_it)
 {
     float* post = (float*)w.lr0;                  // posterior LLR per variable
-    float* cmsg = (float*)w.msg;                  // check->variable message per edge
+    float* cmsg = (float*)w.msg;                  // check->variable message per slot
     for (int v = lane; v < c.n; v += 32) post[v] = w.rx[v];
     __syncwarp();                                 // rx (aliases cmsg) is dead now
-    for (int e = lane; e < c.edges; e += 32) cmsg[e] = 0.f;
+    for (int e = lane; e < c.slots; e += 32) cmsg[e] = 0.f;
     __syncwarp();
     const float norm = 0.8125f;
     int nit = 0;
     while (nit < max_it) {
         nit++;
         for (int r = 0; r < c.m; r++) {
-            const int e0 = c.row_ptr[r], deg = c.row_ptr[r + 1] - e0;
+            const int deg = c.row_len()[r], slot = lane * c.m + r;
             float q = 1e30f; int v = 0; float old = 0.f;
-            if (lane < deg) { v = c.row_var[e0 + lane]; old = cmsg[e0 + lane]; q = post[v] - old; }
+            if (lane < deg) { v = c.row_var()[slot]; old = cmsg[slot]; q = post[v] - old; }
             float a = fabsf(q);
             unsigned sgn = __ballot_sync(0xffffffffu, lane < deg && q < 0.f);
             float m1 = a; int arg = lane;
@@ -330,7 +362,7 @@ __device__ int bp_layered_run(const CodeDev& c, const WarpBuf& w, int lane, int 
                 const float mag = norm * (lane == arg ? m2 : m1);
                 const bool neg = ((__popc(sgn) & 1) != 0) != (q < 0.f);
                 const float nm = neg ? -mag : mag;
-                cmsg[e0 + lane] = nm;
+                cmsg[slot] = nm;
                 post[v] = q + nm;
             }
             __syncwarp();
@@ -342,69 +374,67 @@ __device__ int bp_layered_run(const CodeDev& c, const WarpBuf& w, int lane, int 
     return nit;
 }
 
-// Copies the codes' graph tables into shared memory and returns CodeDev records whose pointers point there
-// (generic addressing).  tab = 2-byte aligned area of `tab_bytes`; falls back to the global tables when they do not fit.
-__device__ void stage_codes(const FecParams& p, CodeDev* scodes, unsigned char* tab)
+// Gather of one codeword: n LLRs of the TB's receive buffer (reads past the received length = 0, shortened positions
+// = -15, tb_decoder.cc:145,161-183), negated and permuted into H column order (ldpc_dec.cc:64-66), plus the hard
+// decisions (awgn_bp::compute_init_estimate).  Segment-major: each segment that overlaps the codeword's LLR range
+// is copied by the whole warp with consecutive lanes on consecutive floats.
+__device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, const CodeS& c, int it, float* rx, uint8_t* est, int lane)
 {
-    const int nthr = blockDim.x;
-    size_t off = 0;
-    for (int ci = 1; ci <= p.n_codes && ci < DTL_MAX_SMEM_CODES; ci++) {
-        const CodeDev g = p.codes[ci];
-        const size_t need = 2 * ((size_t)(g.m + 1) + g.edges + (g.n + 1) + g.edges + g.n);
-        CodeDev sc = g;
-        if (off + need <= (size_t)p.tab_bytes) {
-            uint16_t* d = (uint16_t*)(tab + off);
-            uint16_t* row_ptr = d; d += g.m + 1;
-            uint16_t* row_var = d; d += g.edges;
-            uint16_t* col_ptr = d; d += g.n + 1;
-            uint16_t* col_edge = d; d += g.edges;
-            uint16_t* permute = d;
-            for (int i = threadIdx.x; i <= g.m; i += nthr) row_ptr[i] = g.row_ptr[i];
-            for (int i = threadIdx.x; i < g.edges; i += nthr) { row_var[i] = g.row_var[i]; col_edge[i] = g.col_edge[i]; }
-            for (int i = threadIdx.x; i <= g.n; i += nthr) col_ptr[i] = g.col_ptr[i];
-            for (int i = threadIdx.x; i < g.n; i += nthr) permute[i] = g.permute[i];
-            sc.row_ptr = row_ptr; sc.row_var = row_var; sc.col_ptr = col_ptr; sc.col_edge = col_edge; sc.permute = permute;
-            off += (need + 15) & ~(size_t)15;
-        }
-        if (threadIdx.x == 0) scodes[ci] = sc;
-    }
-    __syncthreads();
-}
-
-__device__ __forceinline__ const CodeDev& code_of(const FecParams& p, const CodeDev* scodes, int fec_id)
-{
-    return fec_id < DTL_MAX_SMEM_CODES ? scodes[fec_id] : p.codes[fec_id];
-}
-
-// Gather of one codeword: n LLRs of the TB's receive buffer (shortened positions = -15, tb_decoder.cc:145,161-183),
-// negated and permuted into H column order (ldpc_dec.cc:64-66), plus the hard decisions (compute_init_estimate).
-__device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, const CodeDev& c, int it, float* rx, uint8_t* est, int lane)
-{
-    const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], ncheck = c.n - c.k;
+    const int rcv_idx = p.cw_geo[3 * it], len = (c.n - c.k) + p.cw_geo[3 * it + 2];
     for (int q = lane; q < c.n; q += 32) {
-        const float v = q < ncheck + k_ ? rcv_at(d, rcv_idx + q, p) : -15.0f;
-        const float x = -1 * v;
-        const int col = c.permute[q];
+        const float x = q < len ? -0.0f : 15.0f;          // -1 * 0 and -1 * -15
+        const int col = c.permute()[q];
         rx[col] = x;
-        est[col] = x < 0.f ? 1 : 0;
+        est[col] = 0;
+    }
+    __syncwarp();
+    const int nseg = d.nseg;
+    int base = 0;
+    for (int i = 0; i < nseg; i++) {
+        const TbSeg sg = d.seg[i];
+        const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+        if (lo < hi) {
+            const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                          : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+            for (int g = lo + lane; g < hi; g += 32) {
+                const float x = -1 * __ldcs(&src[g - base]);
+                const int col = c.permute()[g - rcv_idx];
+                rx[col] = x;
+                est[col] = x < 0.f ? 1 : 0;
+            }
+        }
+        base += sg.len;
     }
     __syncwarp();
 }
 
-// Pass 1, one warp per codeword, tiny footprint (full occupancy, HBM-latency hidden): gather, hard decision, syndrome.
+#define DTL_STAGE_ALL_CODES(p, scodes, sm)                                                         \
+    {                                                                                              \
+        size_t off_ = 0;                                                                           \
+        for (int ci_ = 1; ci_ <= (p).n_codes; ci_++) {                                             \
+            const CodeDev g_ = (p).codes[ci_];                                                     \
+            const CodeS sc_ = stage_code(g_, (sm), (int)off_);                                         \
+            if (threadIdx.x == 0) (scodes)[ci_] = sc_;                                             \
+            off_ += code_tab_bytes(g_.n, g_.m, g_.max_row * g_.m, g_.edges);                       \
+        }                                                                                          \
+        __syncthreads();                                                                           \
+    }
+
+// Pass 1, one warp per codeword, tiny footprint (full occupancy, HBM latency hidden): gather, hard decision, syndrome.
 // A zero syndrome is awgn_bp's exit before the first iteration (nit = 0): the systematic bits go out right away;
 // anything else is queued for the belief-propagation pass.
 __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ CodeDev scodes[DTL_MAX_SMEM_CODES];
+    __shared__ CodeS scodes[DTL_MAX_SMEM_CODES];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
-    stage_codes(p, scodes, sm);
+    DTL_STAGE_ALL_CODES(p, scodes, sm)
     const int total = min(p.cnt[0], p.cw_cap);
     unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.screen_bytes;
     for (int it = blockIdx.x * warps + wid; it < total; it += gridDim.x * warps) {
         const TbDesc& d = p.tbs[p.cw_tb[it]];
-        const CodeDev& c = code_of(p, scodes, d.fec_id);
+        CodeS c = scodes[d.fec_id];
+        c.smb = sm;
         float* rx = (float*)base;
         uint8_t* est = base + (size_t)c.n * 4;
         gather_cw(p, d, c, it, rx, est, lane);
@@ -412,7 +442,7 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
         if (!bad) {
             const int d_idx = p.cw_geo[3 * it + 1], k_ = p.cw_geo[3 * it + 2];
             uint8_t* out = p.bits + d.bit_base + d_idx;
-            for (int q = lane; q < k_; q += 32) out[q] = est[c.permute[c.rank + q]];   // cldpc::get_systematic_bits
+            for (int q = lane; q < k_; q += 32) out[q] = est[c.permute()[c.rank + q]];   // cldpc::get_systematic_bits
             if (lane == 0) p.cw_nit[it] = 0;
         } else if (lane == 0) {
             p.bp_list[atomicAdd(&p.cnt[3], 1)] = it;
@@ -425,9 +455,9 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 __global__ void __launch_bounds__(128, 4) ldpc_bp_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ CodeDev scodes[DTL_MAX_SMEM_CODES];
+    __shared__ CodeS scodes[DTL_MAX_SMEM_CODES];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    stage_codes(p, scodes, sm);
+    DTL_STAGE_ALL_CODES(p, scodes, sm)
     unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.warp_bytes;
     const int total = p.cnt[3];
     for (;;) {
@@ -437,25 +467,27 @@ __global__ void __launch_bounds__(128, 4) ldpc_bp_kernel(FecParams p)
         if (j >= total) break;
         const int it = p.bp_list[j];
         const TbDesc& d = p.tbs[p.cw_tb[it]];
-        const CodeDev& c = code_of(p, scodes, d.fec_id);
-        const WarpBuf w = carve(base, c.n, c.edges);
+        CodeS c = scodes[d.fec_id];
+        c.smb = sm;
+        const WarpBuf w = carve(base, c.n, c.slots);
         gather_cw(p, d, c, it, w.rx, w.est, lane);
         const int nit = p.mode == DTL_LDPC_LAYERED ? bp_layered_run(c, w, lane, p.max_it)
                                                    : bp_reference_run(c, w, lane, p.max_it, p.sigma2);
         const int d_idx = p.cw_geo[3 * it + 1], k_ = p.cw_geo[3 * it + 2];
         uint8_t* out = p.bits + d.bit_base + d_idx;
-        for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute[c.rank + q]];
+        for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
         if (lane == 0) p.cw_nit[it] = nit;
         __syncwarp();
     }
 }
 
-__global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
+__global__ void __launch_bounds__(128, 4) ldpc_plain_kernel(LdpcParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const CodeDev& c = p.code;
-    const WarpBuf w = carve(sm + (size_t)wid * p.warp_bytes, c.n, c.edges);
+    const CodeS c = stage_code(p.code, sm, 0);
+    __syncthreads();
+    const WarpBuf w = carve(sm + p.tab_bytes + (size_t)wid * p.warp_bytes, c.n, c.slots);
     for (;;) {
         long long it = 0;
         if (lane == 0) it = atomicAdd(p.cursor, 1);
@@ -464,7 +496,7 @@ __global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
         const float* in = p.llr + it * c.n;
         for (int q = lane; q < c.n; q += 32) {                                      // ldpc_dec.cc:64-66
             const float x = -1 * in[q];
-            const int col = c.permute[q];
+            const int col = c.permute()[q];
             w.rx[col] = x; w.est[col] = x < 0.f ? 1 : 0;
         }
         __syncwarp();
@@ -472,7 +504,7 @@ __global__ void __launch_bounds__(256) ldpc_plain_kernel(LdpcParams p)
         if (syndrome_nonzero(c, w.est, lane))
             nit = p.mode == DTL_LDPC_LAYERED ? bp_layered_run(c, w, lane, p.max_it) : bp_reference_run(c, w, lane, p.max_it, p.sigma2);
         uint8_t* out = p.bits + it * c.k;
-        for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute[c.rank + q]];
+        for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
         if (lane == 0 && p.nit) p.nit[it] = nit;
         __syncwarp();
     }
@@ -622,15 +654,15 @@ __global__ void cursor_clear_kernel(int* c) { *c = 0; }
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
 {
     if (p.count <= 0) return cudaSuccess;
-    const int warps = 8;
-    const size_t smem = (size_t)p.warp_bytes * warps;
+    const int warps = 4;
+    const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
     static size_t attr_set = 0;
     if (smem > 48 * 1024 && smem > attr_set) {
         cudaFuncSetAttribute(ldpc_plain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = smem;
     }
-    int per_sm = (int)((220 * 1024) / (smem + 1024));
+    int per_sm = (int)((226 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 8) per_sm = 8;
     long long want = (p.count + warps - 1) / warps;
