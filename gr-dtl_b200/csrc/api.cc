@@ -251,6 +251,9 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         for (size_t k = 0; k < occ[oset].size(); k++) ser_src[ser_base[i] + k] = (uint16_t)(i * N + bin_of(occ[oset][k], N, shifted));
     }
     pl.sym_kind = h->upload(sym_kind, e); pl.ser_src = h->upload(ser_src, e);
+    std::vector<double> rcp_tab((size_t)std::max(pprefix[L], 1));
+    for (size_t i = 0; i < rcp_tab.size(); i++) rcp_tab[i] = 1.0 / (double)(i + 1);
+    pl.rcp_tab = h->upload(rcp_tab, e);
 
     // ---- TX allocator tables (digital.ofdm_carrier_allocator_cvc): data symbol s = 0 is the first header symbol
     std::vector<int> tx_base(H + L + 1, 0);

@@ -38,6 +38,7 @@ struct PlanDev {
     const float2* phase_tab;     // [2*max_off+1][L+1]: per-symbol correction i<L, taps rotation at L
     const uint32_t* sym_kind;    // [L][N] bits 0-1: 0 unused / 1 data / 2 pilot; bits 16-31: pilot slot in the frame
     const uint16_t* ser_src;     // [cap] serialised symbol idx -> i*N + bin
+    const double* rcp_tab;       // [npil_frame] RN(1/(i+1)) for the SNR recurrence
 };
 
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.
