@@ -251,6 +251,7 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         for (size_t k = 0; k < occ[oset].size(); k++) ser_src[ser_base[i] + k] = (uint16_t)(i * N + bin_of(occ[oset][k], N, shifted));
     }
     pl.sym_kind = h->upload(sym_kind, e); pl.ser_src = h->upload(ser_src, e);
+    std::vector<uint32_t> h_sym_kind = sym_kind; std::vector<uint16_t> h_ser_src = ser_src;
     std::vector<double> rcp_tab((size_t)std::max(pprefix[L], 1));
     for (size_t i = 0; i < rcp_tab.size(); i++) rcp_tab[i] = 1.0 / (double)(i + 1);
     pl.rcp_tab = h->upload(rcp_tab, e);
@@ -289,6 +290,28 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
     h->cn.off[0] = h->cn.off[1];
     h->cn.off[DTL_CNST_MAX + 1] = (int)pts_all.size();
     h->cn.points = h->upload(pts_all, e); h->cn.inv_points = h->upload(inv_all, e);
+    {   // table blob of eq_demap_kernel (PlanDev::blob)
+        auto al = [](size_t x) { return (x + 15) & ~(size_t)15; };
+        const size_t npil = (size_t)pl.npil_frame;
+        const size_t o_inv = 0, o_ser = al(o_inv + inv_all.size() * 8), o_kind = al(o_ser + (size_t)std::max(h->cap, 1) * 2);
+        const size_t o_pinv = al(o_kind + (size_t)L * N * 2), o_psym = al(o_pinv + npil * 8), total = al(o_psym + npil * 8);
+        std::vector<unsigned char> blob(total, 0);
+        memcpy(&blob[o_inv], inv_all.data(), inv_all.size() * 8);
+        memcpy(&blob[o_ser], h_ser_src.data(), h_ser_src.size() * 2);
+        uint16_t* k16 = (uint16_t*)&blob[o_kind];
+        float2* bpinv = (float2*)&blob[o_pinv]; float2* bpsym = (float2*)&blob[o_psym];
+        for (int i = 0; i < L; i++) {
+            const int pset = nps ? (c->symbols_skipped + i) % nps : 0;
+            for (int b = 0; b < N; b++) {
+                const uint32_t g = h_sym_kind[(size_t)i * N + b];
+                k16[(size_t)i * N + b] = (uint16_t)((g & 3u) | ((g >> 16) << 2));
+                if ((g & 3u) == 2u && nps) { bpinv[g >> 16] = pinv[(size_t)pset * N + b]; bpsym[g >> 16] = psym[(size_t)pset * N + b]; }
+            }
+        }
+        if (pl.npil_frame >= 16384) return fail(h, DTL_ERR_UNSUPPORTED, "more than 16383 pilots per frame");
+        pl.blob = h->upload(blob, e); pl.blob_bytes = (int)total;
+        pl.blob_inv = (int)o_inv; pl.blob_ser = (int)o_ser; pl.blob_kind = (int)o_kind; pl.blob_pinv = (int)o_pinv; pl.blob_psym = (int)o_psym;
+    }
 
     // ---- twiddles exp(-2 pi i j / N), CRC-32 table (poly 0x04C11DB7 reflected, crc_util.cc:23)
     std::vector<float2> tw(N);

@@ -39,6 +39,12 @@ struct PlanDev {
     const uint32_t* sym_kind;    // [L][N] bits 0-1: 0 unused / 1 data / 2 pilot; bits 16-31: pilot slot in the frame
     const uint16_t* ser_src;     // [cap] serialised symbol idx -> i*N + bin
     const double* rcp_tab;       // [npil_frame] RN(1/(i+1)) for the SNR recurrence
+    // the tables eq_demap_kernel touches per symbol, as one 16-byte aligned blob (copied to shared memory by TMA):
+    const unsigned char* blob; int blob_bytes;
+    int blob_inv;                // float2[n_points] 1/point of every constellation (= CnstDev::inv_points)
+    int blob_ser;                // u16[cap]         = ser_src
+    int blob_kind;               // u16[L*N]         kind | pilot slot << 2
+    int blob_pinv, blob_psym;    // float2[npil_frame] 1/pilot and pilot of pilot slot q
 };
 
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.

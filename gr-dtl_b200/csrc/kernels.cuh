@@ -34,7 +34,6 @@ struct EqParams {
     int* err;                                      // device error word (bit 0: bad constellation)
     const float2* tw;
     int use_tma;                                   // set by the launcher: source 16-byte aligned
-    int debug;                                     // DTL_EQ_DEBUG experiment bits (0 in production)
 };
 
 // ---- per-stream sequential bookkeeping ------------------------------------------------------------------
