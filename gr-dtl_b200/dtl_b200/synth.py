@@ -46,8 +46,8 @@ class _Plan:
 
 
 def fec_plan(F, cap, bps, n, k, fec_id=1):
-    """Replays the FEC framer's per-frame decisions (fec_frame_bvb_impl.cc:343-432 restated as in
-    oracle/src/txrx.cc tx_framer::next_frame, which the parity tests pin against the RX side)."""
+    """Replays the FEC framer's per-frame decisions (fec_frame_bvb_impl.cc:343-432); tests/test_synth.py pins the tags
+    against the test-suite's CPU framer and the round trip through the receive path."""
     ncheck = n - k
     p = _Plan()
     meta = np.zeros(F, dtype=frame_meta_dtype)
