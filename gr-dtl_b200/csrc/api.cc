@@ -311,6 +311,36 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         if (pl.npil_frame >= 16384) return fail(h, DTL_ERR_UNSUPPORTED, "more than 16383 pilots per frame");
         pl.blob = h->upload(blob, e); pl.blob_bytes = (int)total;
         pl.blob_inv = (int)o_inv; pl.blob_ser = (int)o_ser; pl.blob_kind = (int)o_kind; pl.blob_pinv = (int)o_pinv; pl.blob_psym = (int)o_psym;
+        // tables of eq_fast_kernel: only when a carrier keeps its role for the whole frame
+        bool uniform = npc >= 1 && nocc >= 1 && nps >= 1 && npil > 0 && npil % L == 0;
+        for (int s = 1; s < nocc && uniform; s++) uniform = occ[s] == occ[0];
+        for (int s = 1; s < npc && uniform; s++)
+            for (int b = 0; b < N; b++)
+                if (pmask[(size_t)s * N + b] != pmask[b] || prank[(size_t)s * N + b] != prank[b]) uniform = false;
+        for (int i = 1; i < L && uniform; i++)
+            for (int b = 0; b < N; b++)
+                if ((h_sym_kind[(size_t)i * N + b] & 3u) != (h_sym_kind[b] & 3u)) uniform = false;
+        pl.fast_ok = uniform ? 1 : 0;
+        pl.pil_per_sym = pl.fast_ok ? (int)npil / L : 0;
+        std::vector<uint8_t> ckind(N, 0);
+        for (int b = 0; b < N; b++) ckind[b] = (uint8_t)(h_sym_kind[b] & 3u);
+        pl.carrier_kind = h->upload(ckind, e);
+        const size_t n_small = (size_t)h->cn.off[DTL_CNST_QAM16 + 1];
+        const size_t f_inv = 0, f_ser = al(f_inv + n_small * 8), f_pinv = al(f_ser + (size_t)std::max(h->cap, 1) * 2);
+        const size_t f_ppos = al(f_pinv + npil * 8), f_rcp = al(f_ppos + npil * 2), f_total = al(f_rcp + npil * 8);
+        std::vector<unsigned char> fb(f_total, 0);
+        memcpy(&fb[f_inv], inv_all.data(), n_small * 8);
+        memcpy(&fb[f_ser], h_ser_src.data(), h_ser_src.size() * 2);
+        memcpy(&fb[f_pinv], bpinv, npil * 8);
+        uint16_t* ppos = (uint16_t*)&fb[f_ppos];
+        for (int i = 0; i < L; i++)
+            for (int b = 0; b < N; b++) {
+                const uint32_t g = h_sym_kind[(size_t)i * N + b];
+                if ((g & 3u) == 2u) ppos[g >> 16] = (uint16_t)(i * N + b);
+            }
+        memcpy(&fb[f_rcp], rcp_tab.data(), npil * 8);
+        pl.fblob = h->upload(fb, e); pl.fblob_bytes = (int)f_total;
+        pl.fb_inv = (int)f_inv; pl.fb_ser = (int)f_ser; pl.fb_pinv = (int)f_pinv; pl.fb_ppos = (int)f_ppos; pl.fb_rcp = (int)f_rcp;
     }
 
     // ---- twiddles exp(-2 pi i j / N), CRC-32 table (poly 0x04C11DB7 reflected, crc_util.cc:23)

@@ -45,6 +45,16 @@ struct PlanDev {
     int blob_ser;                // u16[cap]         = ser_src
     int blob_kind;               // u16[L*N]         kind | pilot slot << 2
     int blob_pinv, blob_psym;    // float2[npil_frame] 1/pilot and pilot of pilot slot q
+    // eq_fast_kernel (one pilot-carrier set, one occupied set: a carrier's role does not change from symbol to symbol)
+    int fast_ok;                 // the plan qualifies
+    int pil_per_sym;             // pilots per OFDM symbol
+    const uint8_t* carrier_kind; // [N] 0 unused / 1 data / 2 pilot
+    const unsigned char* fblob; int fblob_bytes;   // small table blob, one TMA copy per CTA:
+    int fb_inv;                  // float2[30]        1/point of BPSK..16QAM (QAM64/256 come from CnstDev::inv_points)
+    int fb_ser;                  // u16[cap]          = ser_src
+    int fb_pinv;                 // float2[npil_frame] 1/pilot of pilot slot q
+    int fb_ppos;                 // u16[npil_frame]   i*N + bin of pilot slot q
+    int fb_rcp;                  // double[npil_frame] = rcp_tab
 };
 
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.
