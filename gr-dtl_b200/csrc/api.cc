@@ -39,7 +39,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_COUNT
+    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_COUNT
 };
 
 } // namespace
@@ -642,6 +642,8 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr;
     p.bytes = fbytes; p.bytes_stride = h->bytes_stride; p.nbytes = fnbytes; p.crc_ok = fcrc;
     p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
+    p.mag = sg.scratch<float>(SL_MAG, (size_t)n * (size_t)std::max(h->pl.npil_frame, 1));     // |pilot_eq| for snr_tags_kernel
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
     h->prof.begin(DTL_STAGE_EQ, 1);
     CK(launch_eq(h->stream, p));
     h->prof.end();

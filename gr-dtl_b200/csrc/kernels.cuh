@@ -34,6 +34,7 @@ struct EqParams {
     int* err;                                      // device error word (bit 0: bad constellation)
     const float2* tw;
     int use_tma;                                   // set by the launcher: source 16-byte aligned
+    float* mag;                                    // [n_frames][npil_frame] scratch: |pilot_eq| (eq_fast_kernel -> snr_tags_kernel)
 };
 
 // ---- per-stream sequential bookkeeping ------------------------------------------------------------------
