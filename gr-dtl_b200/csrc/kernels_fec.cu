@@ -252,27 +252,71 @@ __device__ __forceinline__ void bp_iter_generic(const CodeS& c, const WarpBuf& w
     __syncwarp();
 }
 
-// The same iteration for row weight <= RMAX and column weight <= CMAX with the per-edge work unrolled and
-// predicated: the divisions of a row (column) are independent instruction chains the scheduler can interleave,
-// and each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
+// IEEE double division without the library routine's per-call reconvergence scaffolding.  ddiv_try() is __ddiv_rn's own
+// fast path, operation for operation (reciprocal seed MUFU.RCP64H with low word 1, two Newton steps, quotient, exact
+// remainder, one correction) and its own acceptance test (the quotient's high word, read as a float, is a normal
+// number and the divisor's is finite); ok == false means the library takes its slow path (zero / infinite / NaN /
+// subnormal operands or results), and the caller then calls __ddiv_rn itself.  The values are therefore the library's
+// in every case; what changes is that several independent divisions can be in flight per thread.
+__device__ __forceinline__ double ddiv_try(double a, double b, bool& ok)
+{
+    double seed;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(b));
+    const double r0 = __hiloint2double(__double2hiint(seed), 1);
+    double e = __fma_rn(-b, r0, 1.0);
+    e = __fma_rn(e, e, e);
+    const double r1 = __fma_rn(r0, e, r0);
+    const double e2 = __fma_rn(-b, r1, 1.0);
+    const double r2 = __fma_rn(r1, e2, r1);
+    const double q0 = __dmul_rn(a, r2);
+    const double rem = __fma_rn(-b, q0, a);
+    const double q = __fma_rn(r2, rem, q0);
+    const float chk = __fmaf_rn(0.0f, __int_as_float(__double2hiint(b)), __int_as_float(__double2hiint(q)));
+    ok = fabsf(chk) > 1.469367938527859385e-39f;
+    return q;
+}
+
+// The same iteration for row weight <= RMAX and column weight <= CMAX with the per-edge work unrolled, branch-free
+// and predicated: the divisions of a row (column) are independent instruction chains the scheduler interleaves, and
+// each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
 template <int RMAX, int CMAX>
 __device__ __forceinline__ void bp_iter_unrolled(const CodeS& c, const WarpBuf& w, int lane)
 {
     for (int r = lane; r < c.m; r += 32) {
         const int deg = c.row_len()[r];
-        double t[RMAX];
+        double den[RMAX], t[RMAX];
+        bool ok[RMAX], all_ok = true;
 #pragma unroll
-        for (int j = 0; j < RMAX; j++)
-            t[j] = j < deg ? __dsub_rn(__ddiv_rn(2.0, __dadd_rn(1.0, w.msg[j * c.m + r])), 1.0) : 1.0;
+        for (int j = 0; j < RMAX; j++) den[j] = j < deg ? __dadd_rn(1.0, w.msg[j * c.m + r]) : 2.0;
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) { t[j] = ddiv_try(2.0, den[j], ok[j]); all_ok &= ok[j]; }
+        if (__builtin_expect(!all_ok, 0)) {
+#pragma unroll
+            for (int j = 0; j < RMAX; j++) if (!ok[j]) t[j] = __ddiv_rn(2.0, den[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) t[j] = j < deg ? __dsub_rn(t[j], 1.0) : 1.0;
         double prod = 1.0;
 #pragma unroll
         for (int j = 0; j < RMAX; j++) if (j < deg) prod = __dmul_rn(prod, t[j]);
+        double pp[RMAX];
+        all_ok = true;
 #pragma unroll
-        for (int j = 0; j < RMAX; j++) {
-            const double pp = __ddiv_rn(prod, t[j]);
-            const double o = __ddiv_rn(__dsub_rn(1.0, pp), __dadd_rn(1.0, pp));
-            if (j < deg) w.msg[j * c.m + r] = o;
+        for (int j = 0; j < RMAX; j++) { pp[j] = ddiv_try(prod, t[j], ok[j]); all_ok &= ok[j]; }
+        if (__builtin_expect(!all_ok, 0)) {
+#pragma unroll
+            for (int j = 0; j < RMAX; j++) if (!ok[j]) pp[j] = __ddiv_rn(prod, t[j]);
         }
+        double o[RMAX];
+        all_ok = true;
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) { o[j] = ddiv_try(__dsub_rn(1.0, pp[j]), __dadd_rn(1.0, pp[j]), ok[j]); all_ok &= ok[j]; }
+        if (__builtin_expect(!all_ok, 0)) {
+#pragma unroll
+            for (int j = 0; j < RMAX; j++) if (!ok[j]) o[j] = __ddiv_rn(__dsub_rn(1.0, pp[j]), __dadd_rn(1.0, pp[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) if (j < deg) w.msg[j * c.m + r] = o[j];
     }
     __syncwarp();
     for (int v = lane; v < c.n; v += 32) {
@@ -283,8 +327,16 @@ __device__ __forceinline__ void bp_iter_unrolled(const CodeS& c, const WarpBuf& 
         double sacc = w.lr0[v];
 #pragma unroll
         for (int j = 0; j < CMAX; j++) if (j < deg) sacc = __dmul_rn(sacc, mv[j]);
+        double o[CMAX];
+        bool ok[CMAX], all_ok = true;
 #pragma unroll
-        for (int j = 0; j < CMAX; j++) { const double o = __ddiv_rn(sacc, mv[j]); if (j < deg) w.msg[e[j]] = o; }
+        for (int j = 0; j < CMAX; j++) { o[j] = ddiv_try(sacc, mv[j], ok[j]); all_ok &= ok[j]; }
+        if (__builtin_expect(!all_ok, 0)) {
+#pragma unroll
+            for (int j = 0; j < CMAX; j++) if (!ok[j]) o[j] = __ddiv_rn(sacc, mv[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < CMAX; j++) if (j < deg) w.msg[e[j]] = o[j];
         w.est[v] = sacc > 1.0 ? 1 : 0;
     }
     __syncwarp();
