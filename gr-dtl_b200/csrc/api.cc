@@ -66,7 +66,7 @@ struct dtl_b200 {
     const float2* d_sync1 = nullptr; const float2* d_sync2 = nullptr;
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
-    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16;
+    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0;
     // per-stream state
     int n_streams = 0;
     DevBuf st_buf, carry_buf, pend_buf;
@@ -327,7 +327,7 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         pl.carrier_kind = h->upload(ckind, e);
         const size_t n_small = (size_t)h->cn.off[DTL_CNST_QAM16 + 1];
         const size_t f_inv = 0, f_ser = al(f_inv + n_small * 8), f_pinv = al(f_ser + (size_t)std::max(h->cap, 1) * 2);
-        const size_t f_ppos = al(f_pinv + npil * 8), f_rcp = al(f_ppos + npil * 2), f_total = al(f_rcp + npil * 8);
+        const size_t f_ppos = al(f_pinv + npil * 8), f_rcp = al(f_ppos + npil * 2), f_total = f_rcp;
         std::vector<unsigned char> fb(f_total, 0);
         memcpy(&fb[f_inv], inv_all.data(), n_small * 8);
         memcpy(&fb[f_ser], h_ser_src.data(), h_ser_src.size() * 2);
@@ -338,7 +338,6 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
                 const uint32_t g = h_sym_kind[(size_t)i * N + b];
                 if ((g & 3u) == 2u) ppos[g >> 16] = (uint16_t)(i * N + b);
             }
-        memcpy(&fb[f_rcp], rcp_tab.data(), npil * 8);
         pl.fblob = h->upload(fb, e); pl.fblob_bytes = (int)f_total;
         pl.fb_inv = (int)f_inv; pl.fb_ser = (int)f_ser; pl.fb_pinv = (int)f_pinv; pl.fb_ppos = (int)f_ppos; pl.fb_rcp = (int)f_rcp;
     }
@@ -393,11 +392,17 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         d.n = code.n; d.m = code.m; d.k = code.k; d.rank = code.rank; d.edges = code.edges; d.max_row = code.max_row; d.max_col = code.max_col;
         d.row_len = h->upload(row_len, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
         d.col_edge = h->upload(col_edge, e); d.permute = h->upload(perm, e);
+        std::vector<uint16_t> inv_perm(code.n, 0), row_wire((size_t)slots, 0);
+        for (int q = 0; q < code.n; q++) inv_perm[perm[q]] = (uint16_t)q;
+        for (int r = 0; r < code.m; r++)
+            for (size_t j = 0; j < code.mlist[r].size(); j++) row_wire[j * code.m + r] = inv_perm[code.mlist[r][j]];
+        d.row_wire = h->upload(row_wire, e);
+        h->screen_tab_bytes += (2 * (code.m + slots) + 15) & ~15;
         d.pmat = h->upload(pmat, e); d.kwords = kwords;
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
         h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, slots));
-        h->screen_bytes = std::max(h->screen_bytes, code.n * 4 + ((code.n + 15) & ~15));
+        h->screen_bytes = std::max(h->screen_bytes, 4 * ((code.n + 31) / 32));
         h->tab_bytes += (int)ldpc_tab_bytes(code.n, code.m, slots, code.edges);
         if (i + 1 >= DTL_MAX_SMEM_CODES || h->tab_bytes > 96 * 1024)
             return fail(h, DTL_ERR_UNSUPPORTED, "too many / too large LDPC codes for the shared-memory graph tables");
@@ -681,7 +686,7 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     p.cw_nit = sg.scratch<int>(SL_CWNIT, (size_t)p.cw_cap);
     p.cw_geo = sg.scratch<int>(SL_CWGEO, (size_t)p.cw_cap * 3);
     p.bp_list = sg.scratch<int>(SL_BPLIST, (size_t)p.cw_cap);
-    p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes;
+    p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes; p.screen_tab_bytes = h->screen_tab_bytes;
     p.bits_cap = (long long)budget * ((long long)h->max_ncws * h->max_k + 4);
     p.bits = sg.scratch<uint8_t>(SL_BITS, (size_t)p.bits_cap + 64);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");

@@ -54,7 +54,7 @@ struct PlanDev {
     int fb_ser;                  // u16[cap]          = ser_src
     int fb_pinv;                 // float2[npil_frame] 1/pilot of pilot slot q
     int fb_ppos;                 // u16[npil_frame]   i*N + bin of pilot slot q
-    int fb_rcp;                  // double[npil_frame] = rcp_tab
+    int fb_rcp;                  // end of the blob (the SNR recurrence's reciprocals are read by snr_tags_kernel from rcp_tab)
 };
 
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.
@@ -65,6 +65,7 @@ struct CodeDev {
     const uint16_t* col_ptr;     // [n+1]
     const uint16_t* col_edge;    // [edges] slots of variable v's edges in nlist order
     const uint16_t* permute;     // [n]
+    const uint16_t* row_wire;    // [max_row*m] WIRE position (inverse permutation) of slot's variable: screening pass
     const uint32_t* pmat;        // [rank][kwords] parity part of the systematic generator, bit j of row i = P[i][j]
     int kwords;                  // ceil(k / 32)
 };

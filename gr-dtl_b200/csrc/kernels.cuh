@@ -65,7 +65,7 @@ struct FecParams {
     int* cw_nit;                                   // [cw_cap]
     int* cw_geo;                                   // [cw_cap][3]: first LLR of the codeword in the TB, first data bit, k_
     int* bp_list;                                  // [cw_cap] codewords that failed the initial syndrome check (cnt[3] of them)
-    int tab_bytes, screen_bytes;                   // shared-memory graph tables; per-warp bytes of the screening pass
+    int tab_bytes, screen_bytes, screen_tab_bytes; // shared-memory graph tables; per-warp bytes and table bytes of the screening pass
     int max_it; double sigma2; int mode; int warp_bytes;
     // outputs
     uint8_t* bytes; int bytes_cap; int* nbytes; dtl_tb_result* tb_out; int tb_cap; int* ntbs;

@@ -472,29 +472,73 @@ __device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, c
         __syncthreads();                                                                           \
     }
 
-// Pass 1, one warp per codeword, tiny footprint (full occupancy, HBM latency hidden): gather, hard decision, syndrome.
-// A zero syndrome is awgn_bp's exit before the first iteration (nit = 0): the systematic bits go out right away;
-// anything else is queued for the belief-propagation pass.
+// Pass 1, one warp per codeword: awgn_bp's exit before the first iteration (zero syndrome of the hard decisions, nit = 0).
+// Works on BITS in wire order: the hard decision of wire position q (ldpc_dec.cc:64-66: rx = -llr, bit = rx < 0, i.e.
+// llr > 0; shortened and missing positions are 0) is one ballot bit, the syndrome uses the graph with cldpc's column
+// permutation folded in (CodeDev::row_wire), and the systematic bits est[permute[rank + i]] are simply wire bits
+// rank.. (cldpc::get_systematic_bits).  No per-codeword floats, 4*ceil(n/32) bytes per warp: full occupancy, the
+// pass streams the LLRs once.  Codewords with a non-zero syndrome are queued for the belief-propagation pass.
 __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ CodeS scodes[DTL_MAX_SMEM_CODES];
+    __shared__ int s_tab[DTL_MAX_SMEM_CODES];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
-    DTL_STAGE_ALL_CODES(p, scodes, sm)
+    {
+        int off = 0;
+        for (int ci = 1; ci <= p.n_codes; ci++) {
+            const CodeDev g = p.codes[ci];
+            const int slots = g.max_row * g.m;
+            uint16_t* rl = (uint16_t*)(sm + off); uint16_t* rw = rl + g.m;
+            for (int i = threadIdx.x; i < g.m; i += blockDim.x) rl[i] = g.row_len[i];
+            for (int i = threadIdx.x; i < slots; i += blockDim.x) rw[i] = g.row_wire[i];
+            if (threadIdx.x == 0) s_tab[ci] = off;
+            off += (2 * (g.m + slots) + 15) & ~15;
+        }
+        __syncthreads();
+    }
     const int total = min(p.cnt[0], p.cw_cap);
-    unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.screen_bytes;
+    uint32_t* estw = (uint32_t*)(sm + p.screen_tab_bytes + (size_t)wid * p.screen_bytes);
     for (int it = blockIdx.x * warps + wid; it < total; it += gridDim.x * warps) {
         const TbDesc& d = p.tbs[p.cw_tb[it]];
-        CodeS c = scodes[d.fec_id];
-        c.smb = sm;
-        float* rx = (float*)base;
-        uint8_t* est = base + (size_t)c.n * 4;
-        gather_cw(p, d, c, it, rx, est, lane);
-        const bool bad = syndrome_nonzero(c, est, lane);
+        const CodeDev& g = p.codes[d.fec_id];
+        const int n = g.n, m = g.m, rank = g.rank, nw = (n + 31) >> 5;
+        const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - g.k) + k_;
+        for (int w = lane; w < nw; w += 32) estw[w] = 0u;
+        __syncwarp();
+        const int nseg = d.nseg;
+        int base = 0;
+        for (int i = 0; i < nseg; i++) {
+            const TbSeg sg = d.seg[i];
+            const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+            if (lo < hi) {
+                const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                              : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                src += rcv_idx - base;                                   // src[pos]: LLR of codeword position pos
+                const int p0 = lo - rcv_idx, p1 = hi - rcv_idx;
+                for (int cb = p0 & ~31; cb < p1; cb += 32) {
+                    const int pos = cb + lane;
+                    bool bit = false;
+                    if (pos >= p0 && pos < p1) bit = __ldcs(&src[pos]) > 0.f;
+                    const unsigned word = __ballot_sync(0xffffffffu, bit);
+                    if (lane == 0 && word) estw[cb >> 5] |= word;
+                }
+            }
+            base += sg.len;
+        }
+        __syncwarp();
+        const uint16_t* rl = (const uint16_t*)(sm + s_tab[d.fec_id]);
+        const uint16_t* rw = rl + m;
+        bool bad = false;
+        for (int r = lane; r < m; r += 32) {
+            const int deg = rl[r];
+            unsigned par = 0;
+            for (int j = 0; j < deg; j++) { const unsigned v = rw[j * m + r]; par ^= estw[v >> 5] >> (v & 31); }
+            bad |= (par & 1u) != 0;
+        }
+        bad = __any_sync(0xffffffffu, bad);
         if (!bad) {
-            const int d_idx = p.cw_geo[3 * it + 1], k_ = p.cw_geo[3 * it + 2];
-            uint8_t* out = p.bits + d.bit_base + d_idx;
-            for (int q = lane; q < k_; q += 32) out[q] = est[c.permute()[c.rank + q]];   // cldpc::get_systematic_bits
+            uint8_t* out = p.bits + d.bit_base + p.cw_geo[3 * it + 1];
+            for (int q = lane; q < k_; q += 32) { const unsigned v = rank + q; out[q] = (uint8_t)((estw[v >> 5] >> (v & 31)) & 1u); }
             if (lane == 0) p.cw_nit[it] = 0;
         } else if (lane == 0) {
             p.bp_list[atomicAdd(&p.cnt[3], 1)] = it;
@@ -504,7 +548,7 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 }
 
 // Pass 2, persistent: each warp pulls queued codewords from a device counter and runs the decoder proper.
-__global__ void __launch_bounds__(128, 4) ldpc_bp_kernel(FecParams p)
+__global__ void __launch_bounds__(128, 5) ldpc_bp_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ CodeS scodes[DTL_MAX_SMEM_CODES];
@@ -667,7 +711,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     tb_plan_kernel<<<(p.n_streams + 127) / 128, 128, 0, st>>>(p);
     prof->end();
     {   // pass 1: screening, grid-stride over the codeword work list
-        const size_t smem = (size_t)p.tab_bytes + 8 * (size_t)p.screen_bytes;
+        const size_t smem = (size_t)p.screen_tab_bytes + 8 * (size_t)p.screen_bytes;
         static size_t attr_set = 0;
         if (smem > 48 * 1024 && smem > attr_set) {
             cudaFuncSetAttribute(ldpc_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
