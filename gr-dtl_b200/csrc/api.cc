@@ -66,7 +66,7 @@ struct dtl_b200 {
     const float2* d_sync1 = nullptr; const float2* d_sync2 = nullptr;
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
-    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0;
+    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
     // per-stream state
     int n_streams = 0;
     DevBuf st_buf, carry_buf, pend_buf;
@@ -392,7 +392,7 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         d.n = code.n; d.m = code.m; d.k = code.k; d.rank = code.rank; d.edges = code.edges; d.max_row = code.max_row; d.max_col = code.max_col;
         d.row_len = h->upload(row_len, e); d.row_var = h->upload(row_var, e); d.col_ptr = h->upload(col_ptr, e);
         d.col_edge = h->upload(col_edge, e); d.permute = h->upload(perm, e);
-        std::vector<uint16_t> inv_perm(code.n, 0), row_wire((size_t)slots, 0);
+        std::vector<uint16_t> inv_perm(code.n, 0), row_wire((size_t)slots, (uint16_t)(32 * ((code.n + 31) / 32)));
         for (int q = 0; q < code.n; q++) inv_perm[perm[q]] = (uint16_t)q;
         for (int r = 0; r < code.m; r++)
             for (size_t j = 0; j < code.mlist[r].size(); j++) row_wire[j * code.m + r] = inv_perm[code.mlist[r][j]];
@@ -402,7 +402,8 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
         h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, slots));
-        h->screen_bytes = std::max(h->screen_bytes, 4 * ((code.n + 31) / 32));
+        h->screen_words = std::max(h->screen_words, (code.n + 31) / 32);
+        h->screen_bytes = (4 * (32 * (h->screen_words + 1) + 32 * h->screen_words + 1) + 15) & ~15;   // est[32][nw+1] + planes
         h->tab_bytes += (int)ldpc_tab_bytes(code.n, code.m, slots, code.edges);
         if (i + 1 >= DTL_MAX_SMEM_CODES || h->tab_bytes > 96 * 1024)
             return fail(h, DTL_ERR_UNSUPPORTED, "too many / too large LDPC codes for the shared-memory graph tables");
@@ -686,7 +687,7 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     p.cw_nit = sg.scratch<int>(SL_CWNIT, (size_t)p.cw_cap);
     p.cw_geo = sg.scratch<int>(SL_CWGEO, (size_t)p.cw_cap * 3);
     p.bp_list = sg.scratch<int>(SL_BPLIST, (size_t)p.cw_cap);
-    p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes; p.screen_tab_bytes = h->screen_tab_bytes;
+    p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes; p.screen_tab_bytes = h->screen_tab_bytes; p.screen_words = h->screen_words;
     p.bits_cap = (long long)budget * ((long long)h->max_ncws * h->max_k + 4);
     p.bits = sg.scratch<uint8_t>(SL_BITS, (size_t)p.bits_cap + 64);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");

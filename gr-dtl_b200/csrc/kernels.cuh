@@ -65,6 +65,7 @@ struct FecParams {
     int* cw_nit;                                   // [cw_cap]
     int* cw_geo;                                   // [cw_cap][3]: first LLR of the codeword in the TB, first data bit, k_
     int* bp_list;                                  // [cw_cap] codewords that failed the initial syndrome check (cnt[3] of them)
+    int screen_words;                              // ceil(max n / 32)
     int tab_bytes, screen_bytes, screen_tab_bytes; // shared-memory graph tables; per-warp bytes and table bytes of the screening pass
     int max_it; double sigma2; int mode; int warp_bytes;
     // outputs

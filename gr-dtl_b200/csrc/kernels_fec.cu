@@ -472,16 +472,33 @@ __device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, c
         __syncthreads();                                                                           \
     }
 
-// Pass 1, one warp per codeword: awgn_bp's exit before the first iteration (zero syndrome of the hard decisions, nit = 0).
-// Works on BITS in wire order: the hard decision of wire position q (ldpc_dec.cc:64-66: rx = -llr, bit = rx < 0, i.e.
-// llr > 0; shortened and missing positions are 0) is one ballot bit, the syndrome uses the graph with cldpc's column
-// permutation folded in (CodeDev::row_wire), and the systematic bits est[permute[rank + i]] are simply wire bits
-// rank.. (cldpc::get_systematic_bits).  No per-codeword floats, 4*ceil(n/32) bytes per warp: full occupancy, the
-// pass streams the LLRs once.  Codewords with a non-zero syndrome are queued for the belief-propagation pass.
+// Pass 1: awgn_bp's exit before the first iteration (zero syndrome of the hard decisions, nit = 0), BIT-SLICED: a warp
+// screens 32 codewords at a time.
+//   * lane l fetches the descriptors of codeword l of the batch (one round of dependent loads for 32 codewords);
+//   * the hard decision of wire position q (ldpc_dec.cc:64-66: rx = -llr, bit = rx < 0, i.e. llr > 0; shortened and
+//     missing positions are 0) is one ballot bit of a coalesced load: est[cw][ceil(n/32)] words in shared memory;
+//   * a 32x32 bit transpose per word column turns them into planes: plane[q] holds bit q of all 32 codewords, so one
+//     XOR per graph edge (CodeDev::row_wire: the graph with cldpc's column permutation folded in) checks a parity
+//     equation of 32 codewords at once, and the OR over the rows is the mask of codewords that need belief propagation;
+//   * the systematic bits est[permute[rank + i]] of a clean codeword are simply wire bits rank.. (get_systematic_bits).
+// Batches that mix codes, and codewords that straddle two LLR segments, take the per-codeword path with the same tables.
+struct ScreenCode { int n, m, k, rank, max_row, tab; };
+
+__device__ __forceinline__ unsigned transpose32(unsigned x, int lane)
+{
+    unsigned m = 0x0000ffffu;
+#pragma unroll
+    for (int j = 16; j != 0; j >>= 1, m ^= (m << j)) {
+        const unsigned y = __shfl_xor_sync(0xffffffffu, x, j);
+        x = (lane & j) ? ((x & (m << j)) | ((y >> j) & m)) : ((x & m) | ((y & m) << j));
+    }
+    return x;
+}
+
 __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ int s_tab[DTL_MAX_SMEM_CODES];
+    __shared__ ScreenCode s_code[DTL_MAX_SMEM_CODES];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
     {
         int off = 0;
@@ -490,58 +507,145 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
             const int slots = g.max_row * g.m;
             uint16_t* rl = (uint16_t*)(sm + off); uint16_t* rw = rl + g.m;
             for (int i = threadIdx.x; i < g.m; i += blockDim.x) rl[i] = g.row_len[i];
-            for (int i = threadIdx.x; i < slots; i += blockDim.x) rw[i] = g.row_wire[i];
-            if (threadIdx.x == 0) s_tab[ci] = off;
+            for (int i = threadIdx.x; i < slots; i += blockDim.x) rw[i] = g.row_wire[i];      // pad slots hold 32*ceil(n/32)
+            if (threadIdx.x == 0) { ScreenCode sc; sc.n = g.n; sc.m = g.m; sc.k = g.k; sc.rank = g.rank; sc.max_row = g.max_row; sc.tab = off; s_code[ci] = sc; }
             off += (2 * (g.m + slots) + 15) & ~15;
         }
         __syncthreads();
     }
     const int total = min(p.cnt[0], p.cw_cap);
-    uint32_t* estw = (uint32_t*)(sm + p.screen_tab_bytes + (size_t)wid * p.screen_bytes);
-    for (int it = blockIdx.x * warps + wid; it < total; it += gridDim.x * warps) {
-        const TbDesc& d = p.tbs[p.cw_tb[it]];
-        const CodeDev& g = p.codes[d.fec_id];
-        const int n = g.n, m = g.m, rank = g.rank, nw = (n + 31) >> 5;
-        const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - g.k) + k_;
-        for (int w = lane; w < nw; w += 32) estw[w] = 0u;
-        __syncwarp();
-        const int nseg = d.nseg;
-        int base = 0;
-        for (int i = 0; i < nseg; i++) {
-            const TbSeg sg = d.seg[i];
-            const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
-            if (lo < hi) {
-                const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
-                                              : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
-                src += rcv_idx - base;                                   // src[pos]: LLR of codeword position pos
-                const int p0 = lo - rcv_idx, p1 = hi - rcv_idx;
-                for (int cb = p0 & ~31; cb < p1; cb += 32) {
-                    const int pos = cb + lane;
-                    bool bit = false;
-                    if (pos >= p0 && pos < p1) bit = __ldcs(&src[pos]) > 0.f;
-                    const unsigned word = __ballot_sync(0xffffffffu, bit);
-                    if (lane == 0 && word) estw[cb >> 5] |= word;
+    const int nwp = p.screen_words + 1;                                   // est row: ceil(n/32) words + one that stays 0
+    uint32_t* estw = (uint32_t*)(sm + p.screen_tab_bytes + (size_t)wid * p.screen_bytes);      // [32][nwp]
+    uint32_t* plane = estw + 32 * nwp;                                    // [32*screen_words + 1]
+    for (int it0 = (blockIdx.x * warps + wid) * 32; it0 < total; it0 += gridDim.x * warps * 32) {
+        const int cnt = min(32, total - it0);
+        // ---- descriptors of codeword it0 + lane
+        int my_fec = 0, my_k = 0, my_p0 = 0, my_p1 = 0, my_single = 1;
+        const float* my_src = nullptr;
+        long long my_out = 0;
+        if (lane < cnt) {
+            const int it = it0 + lane;
+            const TbDesc& d = p.tbs[p.cw_tb[it]];
+            my_fec = d.fec_id;
+            const ScreenCode sc = s_code[my_fec];
+            const int rcv_idx = p.cw_geo[3 * it];
+            my_k = p.cw_geo[3 * it + 2];
+            my_out = d.bit_base + p.cw_geo[3 * it + 1];
+            const int len = (sc.n - sc.k) + my_k, nseg = d.nseg;
+            int base = 0, hits = 0;
+            for (int i = 0; i < nseg; i++) {
+                const TbSeg sg = d.seg[i];
+                const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+                if (lo < hi) {
+                    hits++;
+                    const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                                  : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                    my_src = src + (rcv_idx - base);                     // my_src[pos]: LLR of codeword position pos
+                    my_p0 = lo - rcv_idx; my_p1 = hi - rcv_idx;
+                }
+                base += sg.len;
+            }
+            my_single = hits <= 1;
+        }
+        const int fec0 = __shfl_sync(0xffffffffu, my_fec, 0);
+        const bool uniform = __all_sync(0xffffffffu, lane >= cnt || my_fec == fec0);
+        // ---- hard decisions, one ballot word per 32 wire positions
+        for (int l = 0; l < cnt; l++) {
+            const int fec = __shfl_sync(0xffffffffu, my_fec, l);
+            const int nw = (s_code[fec].n + 31) >> 5;
+            uint32_t* row = estw + l * nwp;
+            if (__shfl_sync(0xffffffffu, my_single, l)) {
+                const float* src = (const float*)__shfl_sync(0xffffffffu, (unsigned long long)my_src, l);
+                const int p0 = __shfl_sync(0xffffffffu, my_p0, l), p1 = __shfl_sync(0xffffffffu, my_p1, l);
+                for (int cb = 0; cb < nw; cb += 4) {                     // four independent loads in flight per lane
+                    float x[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const int pos = (cb + u) * 32 + lane;
+                        x[u] = (pos >= p0 && pos < p1) ? __ldcs(&src[pos]) : 0.f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const unsigned word = __ballot_sync(0xffffffffu, x[u] > 0.f);
+                        if (lane == 0 && cb + u < nw) row[cb + u] = word;
+                    }
+                }
+                if (lane == 0) row[nw] = 0u;
+            } else {                                                      // the codeword straddles LLR segments
+                const int it = it0 + l;
+                const TbDesc& d = p.tbs[p.cw_tb[it]];
+                const ScreenCode sc = s_code[fec];
+                const int rcv_idx = p.cw_geo[3 * it], len = (sc.n - sc.k) + p.cw_geo[3 * it + 2];
+                for (int w = lane; w <= nw; w += 32) row[w] = 0u;
+                __syncwarp();
+                int base = 0;
+                for (int i = 0; i < d.nseg; i++) {
+                    const TbSeg sg = d.seg[i];
+                    const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+                    if (lo < hi) {
+                        const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                                      : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                        src += rcv_idx - base;
+                        const int p0 = lo - rcv_idx, p1 = hi - rcv_idx;
+                        for (int cb = p0 & ~31; cb < p1; cb += 32) {
+                            const int pos = cb + lane;
+                            const bool bit = pos >= p0 && pos < p1 && __ldcs(&src[pos]) > 0.f;
+                            const unsigned word = __ballot_sync(0xffffffffu, bit);
+                            if (lane == 0 && word) row[cb >> 5] |= word;
+                        }
+                    }
+                    base += sg.len;
                 }
             }
-            base += sg.len;
         }
         __syncwarp();
-        const uint16_t* rl = (const uint16_t*)(sm + s_tab[d.fec_id]);
-        const uint16_t* rw = rl + m;
-        bool bad = false;
-        for (int r = lane; r < m; r += 32) {
-            const int deg = rl[r];
-            unsigned par = 0;
-            for (int j = 0; j < deg; j++) { const unsigned v = rw[j * m + r]; par ^= estw[v >> 5] >> (v & 31); }
-            bad |= (par & 1u) != 0;
+        // ---- syndromes
+        unsigned badw = 0;
+        if (uniform) {
+            const ScreenCode sc = s_code[fec0];
+            const int nw = (sc.n + 31) >> 5;
+            for (int w = 0; w < nw; w++) plane[w * 32 + lane] = transpose32(lane < cnt ? estw[lane * nwp + w] : 0u, lane);
+            if (lane == 0) plane[nw * 32] = 0u;
+            __syncwarp();
+            const uint16_t* rw = (const uint16_t*)(sm + sc.tab) + sc.m;
+            for (int r = lane; r < sc.m; r += 32) {
+                const uint16_t* rwr = rw + r;
+                unsigned par = 0;
+#pragma unroll 3
+                for (int j = 0; j < sc.max_row; j++) par ^= plane[rwr[j * sc.m]];
+                badw |= par;
+            }
+            badw = __reduce_or_sync(0xffffffffu, badw);
+        } else {
+            for (int l = 0; l < cnt; l++) {
+                const ScreenCode sc = s_code[__shfl_sync(0xffffffffu, my_fec, l)];
+                const uint16_t* rw = (const uint16_t*)(sm + sc.tab) + sc.m;
+                const uint32_t* row = estw + l * nwp;
+                bool bad = false;
+                for (int r = lane; r < sc.m; r += 32) {
+                    unsigned par = 0;
+                    for (int j = 0; j < sc.max_row; j++) { const unsigned v = rw[j * sc.m + r]; par ^= row[v >> 5] >> (v & 31u); }
+                    bad |= (par & 1u) != 0;
+                }
+                if (__any_sync(0xffffffffu, bad)) badw |= 1u << l;
+            }
         }
-        bad = __any_sync(0xffffffffu, bad);
-        if (!bad) {
-            uint8_t* out = p.bits + d.bit_base + p.cw_geo[3 * it + 1];
-            for (int q = lane; q < k_; q += 32) { const unsigned v = rank + q; out[q] = (uint8_t)((estw[v >> 5] >> (v & 31)) & 1u); }
-            if (lane == 0) p.cw_nit[it] = 0;
-        } else if (lane == 0) {
-            p.bp_list[atomicAdd(&p.cnt[3], 1)] = it;
+        if (cnt < 32) badw &= (1u << cnt) - 1u;
+        // ---- clean codewords: systematic bits out; the rest: queued for the belief-propagation pass
+        for (int l = 0; l < cnt; l++) {
+            if ((badw >> l) & 1u) continue;
+            const int rank = s_code[__shfl_sync(0xffffffffu, my_fec, l)].rank, k_ = __shfl_sync(0xffffffffu, my_k, l);
+            uint8_t* out = p.bits + __shfl_sync(0xffffffffu, my_out, l);
+            const uint32_t* row = estw + l * nwp;
+            for (int q = lane; q < k_; q += 32) { const unsigned v = rank + q; out[q] = (uint8_t)((row[v >> 5] >> (v & 31u)) & 1u); }
+        }
+        if (lane < cnt && !((badw >> lane) & 1u)) p.cw_nit[it0 + lane] = 0;
+        const int n_bad = __popc(badw);
+        if (n_bad) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&p.cnt[3], n_bad);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if ((badw >> lane) & 1u) p.bp_list[base + __popc(badw & ((1u << lane) - 1u))] = it0 + lane;
         }
         __syncwarp();
     }
