@@ -48,99 +48,143 @@ __device__ __forceinline__ void rcv_push(Rcv& r, int src, int start, int len)
     r.nseg++; r.len += len;
 }
 
-__global__ void tb_plan_kernel(FecParams p)
+// One WARP per stream.  Lanes fetch the tags of 32 frames at a time (coalesced); the state machine itself is serial over
+// the frames of a stream and runs replicated in every lane on shuffled tags, so its loop touches no memory it has to
+// wait for.  Released TBs are numbered inside the stream first (codeword index, bit offset); the stream then takes its
+// ranges of the global work lists with ONE atomic per list, and the lanes fill in the TB list and the per-codeword
+// work items (geometry of tb_decoder.cc:161-183 in closed form: the first payload % ncws codewords carry one more bit).
+__global__ void __launch_bounds__(128) tb_plan_kernel(FecParams p)
 {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= p.n_streams) return;
     StreamState st = p.st[s];
     Rcv rcv; rcv_clear(rcv);
     if (st.carry_len > 0) rcv_push(rcv, -1, 0, st.carry_len);
-    int ntb = 0, err = 0;
+    int ntb = 0, err = 0, cw_local = 0;
+    long long bits_local = 0;
 
     auto release = [&](int fec_id, int ncws, int payload_len, int tb_no, int frame_index) {
         const CodeDev& c = p.codes[fec_id];
         if (rcv.bad) { err |= ERR_SEGS; return; }
         if (payload_len < 0 || payload_len > ncws * c.k) { err |= ERR_TB_META; return; }
         if (ntb >= p.tb_slots) { err |= ERR_TB_SLOTS; return; }
-        const int first = atomicAdd(&p.cnt[0], ncws);
-        if (first + ncws > p.cw_cap) { err |= ERR_CW_CAP; return; }
-        const long long bit_base = (long long)atomicAdd(p.bits_used, (unsigned long long)((payload_len + 3) & ~3));
-        if (bit_base + payload_len > p.bits_cap) { err |= ERR_BITS_CAP; return; }
-        const int gi = s * p.tb_slots + ntb;
-        TbDesc& d = p.tbs[gi];
-        d.stream = s; d.fec_id = fec_id; d.ncws = ncws; d.payload_len = payload_len; d.tb_no = tb_no;
-        d.frame_index = frame_index; d.nseg = rcv.nseg; d.cw_first = first; d.bit_base = bit_base;
-        for (int i = 0; i < rcv.nseg; i++) d.seg[i] = rcv.seg[i];
-        int rem = payload_len, rcv_idx = 0, d_idx = 0;                   // codeword geometry (tb_decoder.cc:161-183)
-        for (int i = 0; i < ncws; i++) {
-            int k_ = rem / (ncws - i);
-            if (rem % (ncws - i)) ++k_;
-            p.cw_tb[first + i] = gi;
-            p.cw_geo[3 * (first + i)] = rcv_idx; p.cw_geo[3 * (first + i) + 1] = d_idx; p.cw_geo[3 * (first + i) + 2] = k_;
-            rem -= k_; rcv_idx += (c.n - c.k) + k_; d_idx += k_;
+        if (lane == 0) {
+            TbDesc& d = p.tbs[s * p.tb_slots + ntb];
+            d.stream = s; d.fec_id = fec_id; d.ncws = ncws; d.payload_len = payload_len; d.tb_no = tb_no;
+            d.frame_index = frame_index; d.nseg = rcv.nseg; d.cw_first = cw_local; d.bit_base = bits_local;
+            for (int i = 0; i < rcv.nseg; i++) d.seg[i] = rcv.seg[i];
         }
-        p.tb_list[atomicAdd(&p.cnt[2], 1)] = gi;
+        cw_local += ncws; bits_local += (payload_len + 3) & ~3;
         ntb++;
     };
 
-    for (int j = 0; j < p.F; j++) {
-        const dtl_frame_meta m = p.meta[(long long)s * p.F + j];
-        if (m.payload_len == 0) continue;                                   // frame not emitted / empty (:141-143)
-        const int bps = (m.constellation >= 1 && m.constellation <= DTL_CNST_MAX) ? p.bps_tab[m.constellation] : 0;
-        if (!bps) { err |= ERR_TAGS; continue; }                            // "Tags missing" (:121-126)
-        if (m.fec_id < 1 || m.fec_id > p.n_codes) { err |= ERR_FEC_TAGS; continue; }   // "FEC tags missing" (:136-138)
-        const int frame_index = st.frame_index++;
-        const CodeDev& fc = p.codes[m.fec_id];
-        const int fpl = 8 * m.payload_len, tb_off = 8 * m.tb_offset;       // :147
-        const int frame_len = 8 * ((p.cap * bps + 7) / 8);
-        if (m.tb_no == st.tb_number) {                                      // tb_decoder.cc:57-70
-            if (st.buf_idx + fpl > 2 * p.max_tb) { err |= ERR_CARRY; continue; }
-            rcv_push(rcv, j, 0, fpl);
-            st.buf_idx += fpl;
-            const int ncws = tb_ncws(p.codes[st.info_fec].n, frame_len);
-            const int expected = (fc.n - fc.k) * ncws + m.tb_payload;
-            if (rcv.len >= expected) {
-                release(st.info_fec, ncws, st.info_tb_payload, m.tb_no, frame_index);
-                st.buf_idx = 0; rcv_clear(rcv);
-            }
-        } else if (rcv.len == 0 && tb_off == fpl) {                         // :75-89
-            st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
-            st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
-            rcv_clear(rcv);
-            rcv_push(rcv, j, 0, tb_off);
-            release(m.fec_id, tb_ncws(fc.n, frame_len), m.tb_payload, m.tb_no, frame_index);
-            rcv_clear(rcv);
-        } else {                                                            // :92-133
-            if (tb_off > 0) rcv_push(rcv, j, 0, tb_off);
-            if (rcv.len > 0 && st.have_info)
-                release(st.info_fec, tb_ncws(p.codes[st.info_fec].n, frame_len), st.info_tb_payload, st.info_tb_number,
-                        frame_index);
-            st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
-            st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
-            rcv_clear(rcv);
-            int extra = 0;
-            if (tb_off % bps) extra = bps - tb_off % bps;
-            const int new_off = tb_off ? tb_off + extra : 0;
-            rcv_push(rcv, j, new_off, fpl + extra - new_off);
-            st.buf_idx += fpl - tb_off;
-            const int ncws = tb_ncws(fc.n, frame_len);
-            const int tb_size = 8 * ((ncws * (fc.n - fc.k) + m.tb_payload + 7) / 8);
-            if (fpl - tb_off == tb_size) {
-                release(m.fec_id, ncws, m.tb_payload, m.tb_no, frame_index);
-                st.buf_idx = 0; rcv_clear(rcv);
+    for (int j0 = 0; j0 < p.F; j0 += 32) {
+        dtl_frame_meta mine;
+        mine.constellation = 0; mine.payload_len = 0; mine.fec_id = 0; mine.tb_no = 0; mine.tb_offset = 0; mine.tb_payload = 0;
+        if (j0 + lane < p.F) mine = p.meta[(long long)s * p.F + j0 + lane];
+        const int jn = min(32, p.F - j0);
+        for (int jj = 0; jj < jn; jj++) {
+            const int j = j0 + jj;
+            dtl_frame_meta m;
+            m.payload_len = __shfl_sync(0xffffffffu, mine.payload_len, jj);
+            if (m.payload_len == 0) continue;                                   // frame not emitted / empty (:141-143)
+            m.constellation = __shfl_sync(0xffffffffu, mine.constellation, jj);
+            m.fec_id = __shfl_sync(0xffffffffu, mine.fec_id, jj);
+            m.tb_no = __shfl_sync(0xffffffffu, mine.tb_no, jj);
+            m.tb_offset = __shfl_sync(0xffffffffu, mine.tb_offset, jj);
+            m.tb_payload = __shfl_sync(0xffffffffu, mine.tb_payload, jj);
+            const int bps = (m.constellation >= 1 && m.constellation <= DTL_CNST_MAX) ? p.bps_tab[m.constellation] : 0;
+            if (!bps) { err |= ERR_TAGS; continue; }                            // "Tags missing" (:121-126)
+            if (m.fec_id < 1 || m.fec_id > p.n_codes) { err |= ERR_FEC_TAGS; continue; }   // "FEC tags missing" (:136-138)
+            const int frame_index = st.frame_index++;
+            const CodeDev& fc = p.codes[m.fec_id];
+            const int fpl = 8 * m.payload_len, tb_off = 8 * m.tb_offset;       // :147
+            const int frame_len = 8 * ((p.cap * bps + 7) / 8);
+            if (m.tb_no == st.tb_number) {                                      // tb_decoder.cc:57-70
+                if (st.buf_idx + fpl > 2 * p.max_tb) { err |= ERR_CARRY; continue; }
+                rcv_push(rcv, j, 0, fpl);
+                st.buf_idx += fpl;
+                const int ncws = tb_ncws(p.codes[st.info_fec].n, frame_len);
+                const int expected = (fc.n - fc.k) * ncws + m.tb_payload;
+                if (rcv.len >= expected) {
+                    release(st.info_fec, ncws, st.info_tb_payload, m.tb_no, frame_index);
+                    st.buf_idx = 0; rcv_clear(rcv);
+                }
+            } else if (rcv.len == 0 && tb_off == fpl) {                         // :75-89
+                st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
+                st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
+                rcv_clear(rcv);
+                rcv_push(rcv, j, 0, tb_off);
+                release(m.fec_id, tb_ncws(fc.n, frame_len), m.tb_payload, m.tb_no, frame_index);
+                rcv_clear(rcv);
+            } else {                                                            // :92-133
+                if (tb_off > 0) rcv_push(rcv, j, 0, tb_off);
+                if (rcv.len > 0 && st.have_info)
+                    release(st.info_fec, tb_ncws(p.codes[st.info_fec].n, frame_len), st.info_tb_payload, st.info_tb_number,
+                            frame_index);
+                st.info_fec = m.fec_id; st.info_tb_payload = m.tb_payload; st.info_tb_number = m.tb_no; st.have_info = 1;
+                st.tb_number = m.tb_no; st.tb_payload_len = m.tb_payload; st.buf_idx = 0;
+                rcv_clear(rcv);
+                int extra = 0;
+                if (tb_off % bps) extra = bps - tb_off % bps;
+                const int new_off = tb_off ? tb_off + extra : 0;
+                rcv_push(rcv, j, new_off, fpl + extra - new_off);
+                st.buf_idx += fpl - tb_off;
+                const int ncws = tb_ncws(fc.n, frame_len);
+                const int tb_size = 8 * ((ncws * (fc.n - fc.k) + m.tb_payload + 7) / 8);
+                if (fpl - tb_off == tb_size) {
+                    release(m.fec_id, ncws, m.tb_payload, m.tb_no, frame_index);
+                    st.buf_idx = 0; rcv_clear(rcv);
+                }
             }
         }
     }
     // what is left belongs to the TB in flight: carry_save_kernel moves it to the carry buffer
-    TbDesc& pd = p.pend[s];
-    pd.nseg = rcv.nseg; pd.stream = s;
-    for (int i = 0; i < rcv.nseg; i++) pd.seg[i] = rcv.seg[i];
     if (rcv.bad) err |= ERR_SEGS;
-    if (rcv.len > p.carry_cap) { err |= ERR_CARRY; pd.nseg = 0; st.carry_len = 0; }
-    else st.carry_len = rcv.len;
-    p.tb_count[s] = ntb;
-    p.st[s] = st;
-    if (err) atomicOr(p.err, err);
+    const bool carry_over = rcv.len > p.carry_cap;
+    if (carry_over) err |= ERR_CARRY;
+    st.carry_len = carry_over ? 0 : rcv.len;
+    if (lane == 0) {
+        TbDesc& pd = p.pend[s];
+        pd.nseg = carry_over ? 0 : rcv.nseg; pd.stream = s;
+        for (int i = 0; i < rcv.nseg; i++) pd.seg[i] = rcv.seg[i];
+        p.tb_count[s] = ntb;
+        p.st[s] = st;
+    }
+
+    // ---- the stream's ranges of the global lists, then the work items
+    int cw_base = 0, tb_base = 0;
+    long long bit_base = 0;
+    if (lane == 0 && ntb) {
+        cw_base = atomicAdd(&p.cnt[0], cw_local);
+        bit_base = (long long)atomicAdd(p.bits_used, (unsigned long long)bits_local);
+        tb_base = atomicAdd(&p.cnt[2], ntb);
+    }
+    cw_base = __shfl_sync(0xffffffffu, cw_base, 0);
+    bit_base = __shfl_sync(0xffffffffu, bit_base, 0);
+    tb_base = __shfl_sync(0xffffffffu, tb_base, 0);
+    if (ntb && cw_base + cw_local > p.cw_cap) err |= ERR_CW_CAP;
+    if (ntb && bit_base + bits_local > p.bits_cap) { err |= ERR_BITS_CAP; bit_base = 0; bits_local = 0; }   // failing call: stay in bounds
+    __syncwarp();
+    for (int i = 0; i < ntb; i++) {
+        const int gi = s * p.tb_slots + i;
+        TbDesc& d = p.tbs[gi];
+        const int ncws = d.ncws, payload_len = d.payload_len, first = cw_base + d.cw_first;
+        const long long bb = bits_local ? bit_base + d.bit_base : 0;
+        const CodeDev& c = p.codes[d.fec_id];
+        const int nk = c.n - c.k, q = payload_len / ncws, r = payload_len - q * ncws;
+        __syncwarp();
+        if (lane == 0) { d.cw_first = first; d.bit_base = bb; p.tb_list[tb_base + i] = gi; }
+        for (int cw = lane; cw < ncws; cw += 32) {
+            const int it = first + cw;
+            if (it >= p.cw_cap) break;
+            const int mn = min(cw, r);
+            p.cw_tb[it] = gi;
+            p.cw_geo[3 * it] = cw * nk + cw * q + mn; p.cw_geo[3 * it + 1] = cw * q + mn; p.cw_geo[3 * it + 2] = q + (cw < r ? 1 : 0);
+        }
+    }
+    if (err && lane == 0) atomicOr(p.err, err);
 }
 
 // ---- awgn_bp::decode for one codeword per warp ---------------------------------------------------------------
@@ -711,19 +755,26 @@ __global__ void __launch_bounds__(128, 4) ldpc_plain_kernel(LdpcParams p)
 }
 
 // ---- TB epilogue: bits -> bytes LSB-first, CRC-32 verify (fec_decoder_impl.cc:161-204) -------------------------
-// One warp per released TB.  The TB's bits (one per byte) are packed in place: the 32 bits of word w are
-// read by the 32 lanes before lane 0 overwrites bytes [4w, 4w+4), which only cover bits already consumed.
+// One warp per released TB.  The TB's bits (one per byte) are packed in place, 32 bits per lane and round: a lane
+// loads its 32 bit-bytes as eight words, folds each into a nibble with one multiply ((x & 0x01010101) * 0x01020408
+// puts bit-byte i at bit 24+i without carries) and writes the packed word after the warp has finished reading the
+// round (the bytes a round overwrites only hold bits of this or earlier rounds).  CRC-32 runs four bytes per step
+// (slicing-by-4 tables in shared memory) on the words the lanes already hold.
 __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
 {
-    __shared__ uint32_t crc_tab[256];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) crc_tab[i] = p.crc_table[i];
+    __shared__ uint32_t crc_tab[4][256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        uint32_t c = p.crc_table[i];
+        crc_tab[0][i] = c;
+        for (int k = 1; k < 4; k++) { c = p.crc_table[c & 0xffu] ^ (c >> 8); crc_tab[k][i] = c; }
+    }
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= p.cnt[2]) return;
     const int gi = p.tb_list[t];
     const TbDesc& d = p.tbs[gi];
-    uint8_t* bits = p.bits + d.bit_base;
+    uint8_t* bits = p.bits + d.bit_base;                       // 4-byte aligned (bit offsets are multiples of 4)
     const int user = d.payload_len - 32;
     int nit_sum = 0;
     for (int i = lane; i < d.ncws; i += 32) nit_sum += p.cw_nit[d.cw_first + i];
@@ -734,54 +785,83 @@ __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
     if (user >= 0) {
         const uint32_t stored = __ballot_sync(0xffffffffu, bits[user + lane] & 1);   // little-endian CRC field
         __syncwarp();
-        const int words = (user + 31) >> 5;
-        for (int w = 0; w < words; w++) {
-            const int b = w * 32 + lane;
-            const uint32_t word = __ballot_sync(0xffffffffu, b < user && (bits[b] & 1));
-            __syncwarp();
-            if (lane == 0) ((uint32_t*)bits)[w] = word;
-            __syncwarp();
-        }
-        const int n0 = (user + 7) >> 3;
+        const int words = (user + 31) >> 5, n0 = (user + 7) >> 3;
+        const uint32_t* bw = (const uint32_t*)bits;
         uint32_t crc = 0xFFFFFFFFu;
-        if (lane == 0) {
-            for (int b = 0; b < n0; b++) crc = crc_tab[(crc ^ bits[b]) & 0xffu] ^ (crc >> 8);
-            crc = ~crc;
+        for (int w0 = 0; w0 < words; w0 += 32) {
+            const int w = w0 + lane;
+            uint32_t word = 0;
+            if (w < words) {
+                const int nb = min(32, user - 32 * w);                          // valid bits of this word
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    uint32_t x = 4 * q < nb ? __ldcg(&bw[8 * w + q]) & 0x01010101u : 0u;
+                    if (nb - 4 * q < 4 && 4 * q < nb) x &= 0xffffffffu >> (8 * (4 - (nb - 4 * q)));
+                    word |= (((x * 0x01020408u) >> 24) & 0xfu) << (4 * q);
+                }
+            }
+            __syncwarp();
+            if (w < words) ((uint32_t*)bits)[w] = word;
+            const int nw = min(32, words - w0);
+            for (int i = 0; i < nw; i++) {                                      // all lanes in step: crc is warp-uniform
+                const uint32_t x = __shfl_sync(0xffffffffu, word, i);
+                const int nby = min(4, n0 - 4 * (w0 + i));
+                if (nby == 4) {
+                    const uint32_t y = crc ^ x;
+                    crc = crc_tab[3][y & 0xffu] ^ crc_tab[2][(y >> 8) & 0xffu] ^ crc_tab[1][(y >> 16) & 0xffu] ^ crc_tab[0][y >> 24];
+                } else {
+                    for (int b = 0; b < nby; b++) crc = crc_tab[0][(crc ^ (x >> (8 * b))) & 0xffu] ^ (crc >> 8);
+                }
+            }
+            __syncwarp();
         }
-        crc = __shfl_sync(0xffffffffu, crc, 0);
+        crc = ~crc;
         r.crc_ok = crc == stored;
         r.nbytes = r.crc_ok ? user >> 3 : 0;
     }
     if (lane == 0) p.tres[gi] = r;
 }
 
-// One warp per stream: concatenate the payload bytes of its CRC-passing TBs in release order
-// (ofdm_adaptive_fec_pack_bb) and compact the per-TB monitor records.
-__global__ void __launch_bounds__(256) tb_gather_kernel(FecParams p)
+// One CTA per stream: concatenate the payload bytes of its CRC-passing TBs in release order
+// (ofdm_adaptive_fec_pack_bb) and compact the per-TB monitor records.  Threads fetch the TB records in parallel, one
+// thread lays the bytes out, then every warp copies its share of the TBs.
+#define DTL_GATHER_MAXTB 1024
+__global__ void __launch_bounds__(128) tb_gather_kernel(FecParams p)
 {
-    const int lane = threadIdx.x & 31;
-    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (s >= p.n_streams) return;
-    const int ntb = p.tb_count[s];
-    int pos = 0, err = 0;
-    for (int i = 0; i < ntb; i++) {
+    __shared__ int s_nb[DTL_GATHER_MAXTB], s_pos[DTL_GATHER_MAXTB + 1];
+    __shared__ long long s_bb[DTL_GATHER_MAXTB];
+    const int s = blockIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    const int ntb = min(p.tb_count[s], DTL_GATHER_MAXTB);
+    for (int i = threadIdx.x; i < ntb; i += blockDim.x) {
         const int gi = s * p.tb_slots + i;
         const dtl_tb_result r = p.tres[gi];
-        if (p.tb_out && i < p.tb_cap && lane == 0) p.tb_out[(size_t)s * p.tb_cap + i] = r;
-        if (r.nbytes > 0 && p.bytes) {
-            if (pos + r.nbytes <= p.bytes_cap) {
-                const uint8_t* src = p.bits + p.tbs[gi].bit_base;
-                uint8_t* dst = p.bytes + (size_t)s * p.bytes_cap + pos;
-                for (int b = lane; b < r.nbytes; b += 32) dst[b] = src[b];
-            } else err = ERR_BITS_CAP;
-        }
-        pos += r.nbytes;
+        if (p.tb_out && i < p.tb_cap) p.tb_out[(size_t)s * p.tb_cap + i] = r;
+        s_nb[i] = r.nbytes; s_bb[i] = p.tbs[gi].bit_base;
     }
-    if (p.tb_out && ntb > p.tb_cap) err |= ERR_TB_SLOTS;
-    if (lane == 0) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int pos = 0, err = 0;
+        for (int i = 0; i < ntb; i++) {
+            s_pos[i] = pos;
+            if (s_nb[i] > 0 && p.bytes && pos + s_nb[i] > p.bytes_cap) { err = ERR_BITS_CAP; s_nb[i] = 0 - s_nb[i]; }
+            pos += s_nb[i] < 0 ? -s_nb[i] : s_nb[i];
+        }
+        s_pos[ntb] = pos;
+        if (p.tb_out && p.tb_count[s] > p.tb_cap) err |= ERR_TB_SLOTS;
+        if (p.tb_count[s] > DTL_GATHER_MAXTB) err |= ERR_TB_SLOTS;
         if (p.nbytes) p.nbytes[s] = pos;
-        if (p.ntbs) p.ntbs[s] = ntb;
+        if (p.ntbs) p.ntbs[s] = p.tb_count[s];
         if (err) atomicOr(p.err, err);
+    }
+    __syncthreads();
+    if (!p.bytes) return;
+    for (int i = wid; i < ntb; i += warps) {
+        const int n = s_nb[i];
+        if (n <= 0) continue;
+        const uint8_t* src = p.bits + s_bb[i];
+        uint8_t* dst = p.bytes + (size_t)s * p.bytes_cap + s_pos[i];
+        for (int b = lane; b < n; b += 32) dst[b] = src[b];
     }
 }
 
@@ -812,7 +892,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     Prof none; if (!prof) prof = &none;
     prof->begin(DTL_STAGE_TBPLAN, 2);
     fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
-    tb_plan_kernel<<<(p.n_streams + 127) / 128, 128, 0, st>>>(p);
+    tb_plan_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
     prof->end();
     {   // pass 1: screening, grid-stride over the codeword work list
         const size_t smem = (size_t)p.screen_tab_bytes + 8 * (size_t)p.screen_bytes;
@@ -842,7 +922,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     const int tb_max = p.n_streams * p.tb_slots;
     prof->begin(DTL_STAGE_TBFINISH, 3);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
-    tb_gather_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
+    tb_gather_kernel<<<p.n_streams, 128, 0, st>>>(p);
     carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     prof->end();
     if (launches) *launches += 7;
