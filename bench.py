@@ -338,8 +338,8 @@ def run_b200(a):
             stage_tab[name] = row
     eq_ms = stages["eq_demap"][0] / max(1, stages["eq_demap"][1])
     achieved = alg["eq_demap"] * frames / (eq_ms * 1e-3) / 1e9
-    traffic_pf = ncu_traffic("eq_demap_kernel")
-    roofline = {"kernel": "eq_demap_kernel (frame equaliser + serialiser + soft demapper)", "bound": "hbm",
+    traffic_pf = ncu_traffic("eq_fast_kernel")
+    roofline = {"kernel": "eq_fast_kernel + snr_tags_kernel (frame equaliser + serialiser + soft demapper; whole stage timed)", "bound": "hbm",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None if traffic_pf is None else traffic_pf * frames,
                 "alg_bytes_per_launch": alg["eq_demap"] * frames, "ms_per_launch": eq_ms, "peak_source": peak_src}

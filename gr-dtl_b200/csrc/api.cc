@@ -650,8 +650,9 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
     p.mag = sg.scratch<float>(SL_MAG, (size_t)n * (size_t)std::max(h->pl.npil_frame, 1));     // |pilot_eq| for snr_tags_kernel
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
+    int eq_launches = 0;
     h->prof.begin(DTL_STAGE_EQ, 1);
-    CK(launch_eq(h->stream, p));
+    CK(launch_eq(h->stream, p, &eq_launches));
     h->prof.end();
     StreamParams sp;
     sp.st = (StreamState*)h->st_buf.p + h->s_off; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
@@ -660,7 +661,7 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     h->prof.begin(DTL_STAGE_STATE, 1);
     CK(launch_stream_state(h->stream, sp));
     h->prof.end();
-    h->launches += 2;
+    h->launches += eq_launches + 1;
     return DTL_OK;
 }
 

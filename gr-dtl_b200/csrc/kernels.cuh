@@ -87,7 +87,7 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
                            long long in_frame_stride, int in_sym0, int in_sym_stride, int in_skip, int N, const float2* tw);
 cudaError_t launch_fft_inv(cudaStream_t st, const float2* in, float2* out, long long n_sym, int N, const float2* tw);
 cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p);
-cudaError_t launch_eq(cudaStream_t st, const EqParams& p);
+cudaError_t launch_eq(cudaStream_t st, const EqParams& p, int* launches = nullptr);   // *launches += kernels launched
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
 cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof);
