@@ -206,10 +206,16 @@ class ofdm_receiver:
         import torch
         if isinstance(dtype, np.dtype) and dtype.fields is not None:
             n = int(np.prod(shape)) * dtype.itemsize
-            return torch.zeros(n, dtype=torch.uint8, device="cuda:%d" % self.device)
+            t = torch.zeros(n, dtype=torch.uint8, device="cuda:%d" % self.device)
+            torch.cuda.current_stream(t.device).synchronize()
+            return t
         tdt = {np.dtype(np.float32): torch.float32, np.dtype(np.complex64): torch.complex64, np.dtype(np.uint8): torch.uint8,
                np.dtype(np.int32): torch.int32, np.dtype(np.float64): torch.float64}[np.dtype(dtype)]
-        return torch.zeros(shape, dtype=tdt, device="cuda:%d" % self.device)
+        t = torch.zeros(shape, dtype=tdt, device="cuda:%d" % self.device)
+        # the fill runs on torch's current stream, the library works on its own: without this a large fill can land
+        # after (on top of) what the library's kernels wrote
+        torch.cuda.current_stream(t.device).synchronize()
+        return t
 
     # ---- stage 1: header_payload_demux (CP strip) + fft_vcc (ofdm_receiver.py:79-86,153) -----------------
     def demod(self, iq, out=None):
