@@ -39,7 +39,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_COUNT
+    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES, SL_COUNT
 };
 
 } // namespace
@@ -66,6 +66,7 @@ struct dtl_b200 {
     const float2* d_sync1 = nullptr; const float2* d_sync2 = nullptr;
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
+    HdrDev hd{}; bool have_hdr = false;   // header branch tables (need the sync words)
     int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
     // per-stream state
     int n_streams = 0;
@@ -276,6 +277,42 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         std::vector<float2> s1(N), s2(N);
         for (int i = 0; i < N; i++) { s1[i] = make_float2(c->sync_word1[2 * i], c->sync_word1[2 * i + 1]); s2[i] = make_float2(c->sync_word2[2 * i], c->sync_word2[2 * i + 1]); }
         h->d_sync1 = h->upload(s1, e); h->d_sync2 = h->upload(s2, e); h->have_sync = true;
+        // ---- header branch (python/dtl/ofdm_receiver.py:100-150): ofdm_chanest_vcvc(sync_word1, sync_word2, header_len),
+        // ofdm_adaptive_header_equalizer (symbols_skipped 0), ofdm_serializer_vcc (symbols_skipped 0), header parser
+        HdrDev& hd = h->hd;
+        hd.N = N; hd.H = H; hd.has_fec = h->fec_enabled;
+        hd.nbits = H * (int)occ[0].size();                  // ofdm_receiver.py:129-130: [occupied_carriers[0]] * header_len
+        int first = 0, last = N - 1;
+        for (int i = 0; i < N; i++) if (s2[i].x != 0.f || s2[i].y != 0.f) { first = i; break; }
+        for (int i = N - 1; i >= 0; i--) if (s2[i].x != 0.f || s2[i].y != 0.f) { last = i; break; }
+        hd.max_neg = -first; hd.max_pos = N - last - 1;
+        if (hd.max_neg % 2) hd.max_neg++;                    // carrier offsets must be even
+        if (hd.max_pos % 2) hd.max_pos--;
+        std::vector<float2> corr(N, make_float2(0, 0));
+        for (int i = 0; i < N; i++)
+            if (s1[i].x != 0.f || s1[i].y != 0.f) {          // sync2 / sync1 in this library's fp32 division contract
+                const float den = std::fmaf(s1[i].x, s1[i].x, s1[i].y * s1[i].y), r = 1.0f / den;
+                const float nr = std::fmaf(s2[i].x, s1[i].x, s2[i].y * s1[i].y), ni = std::fmaf(s2[i].y, s1[i].x, -(s2[i].x * s1[i].y));
+                corr[i] = make_float2(nr * r, ni * r);
+            }
+        std::vector<uint8_t> hkind((size_t)H * N, 0);
+        std::vector<float2> hpinv((size_t)H * N, make_float2(0, 0));
+        std::vector<uint16_t> hser;
+        for (int i = 0; i < H; i++) {
+            const int pcs = npc ? i % npc : 0, pss = nps ? i % nps : 0;
+            for (int b = 0; b < N; b++) {
+                if (npc && pmask[(size_t)pcs * N + b]) { hkind[(size_t)i * N + b] = 2; if (nps) hpinv[(size_t)i * N + b] = pinv[(size_t)pss * N + b]; }
+                else if (occupied[b]) hkind[(size_t)i * N + b] = 1;
+            }
+            const auto& oset = occ[i % nocc];
+            for (size_t k = 0; k < oset.size(); k++) hser.push_back((uint16_t)(i * N + bin_of(oset[k], N, shifted)));
+        }
+        hser.resize((size_t)hd.nbits, 0);
+        std::vector<float2> hrot((size_t)2 * pl.max_off + 1);
+        for (int off = -pl.max_off; off <= pl.max_off; off++) hrot[(size_t)(off + pl.max_off)] = expj_contract((2.0 * M_PI) * off * h->cp / N * H);
+        hd.ref = h->d_sync2; hd.corr_v = h->upload(corr, e); hd.kind = h->upload(hkind, e); hd.pinv = h->upload(hpinv, e);
+        hd.ser = h->upload(hser, e); hd.rot = h->upload(hrot, e);
+        h->have_hdr = (size_t)H * N <= 65535;
     }
 
     // ---- constellations
@@ -1028,6 +1065,77 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
     int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
     s = rx_device(h, sg, in_kind, d_in, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
+    if (s != DTL_OK) return s;
+    return sg.finish();
+}
+
+// ---- header branch ---------------------------------------------------------------------------------------------------------------------
+namespace {
+dtl_status dev_header(dtl_b200* h, Stage& sg, const float2* d_iq, int S, int F, dtl_frame_meta* d_meta, float2* d_taps,
+                      dtl_header_result* d_hres)
+{
+    if (!h->have_hdr) return fail(h, DTL_ERR_INVALID_ARG, "header branch needs the sync words (and header_syms * fft_len <= 65535)");
+    const long long n = (long long)S * F;
+    float2* hfreq = sg.scratch<float2>(SL_HFREQ, (size_t)n * (2 + h->H) * h->N);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
+    h->prof.begin(DTL_STAGE_HEADER, 1);
+    CK(launch_fft_fwd(h->stream, d_iq, hfreq, n * (2 + h->H), 2 + h->H, h->frame_samples, 0, h->N + h->cp, h->cp, h->N, h->tw));
+    HdrParams p;
+    memset(&p, 0, sizeof p);
+    p.hd = h->hd; p.pl = h->pl; p.cn = h->cn; p.hfreq = hfreq; p.n_frames = n; p.n_streams = S; p.F = F;
+    p.meta = d_meta; p.taps = d_taps; p.hres = d_hres; p.st = (StreamState*)h->st_buf.p + h->s_off;
+    CK(launch_header(h->stream, p));
+    h->prof.end();
+    h->launches += 3;
+    return DTL_OK;
+}
+} // namespace
+
+extern "C" dtl_status dtl_b200_rx_headers(dtl_b200* h, const float* iq, int32_t n_streams, int32_t frames_per_stream,
+                                          dtl_frame_meta* meta, float* taps, dtl_header_result* hres, int mem)
+{
+    if (!h || !iq || !meta || n_streams < 0 || frames_per_stream < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    const int S = n_streams, F = frames_per_stream;
+    const size_t n = (size_t)S * F;
+    dtl_status s = ensure_streams(h, S);
+    if (s != DTL_OK) return s;
+    Stage sg(h, mem);
+    const float2* d_iq = sg.in(SL_IQ, (const float2*)iq, n * h->frame_samples);
+    dtl_frame_meta* d_meta = sg.out(SL_HMETA, meta, n);
+    float2* d_taps = sg.out(SL_HTAPS, (float2*)taps, n * h->N);
+    dtl_header_result* d_hres = sg.out(SL_HRES, hres, n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
+    return sg.finish();
+}
+
+extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_streams, int32_t frames_per_stream,
+                                     dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
+                                     uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                                     dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem)
+{
+    if (!h || !iq || n_streams < 0 || frames_per_stream < 0) return DTL_ERR_INVALID_ARG;
+    if ((bytes && bytes_cap <= 0) || (tbs && tb_cap <= 0)) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    const int S = n_streams, F = frames_per_stream;
+    const size_t n = (size_t)S * F;
+    dtl_status s = ensure_streams(h, S);
+    if (s != DTL_OK) return s;
+    Stage sg(h, mem);
+    const float2* d_iq = sg.in(SL_IQ, (const float2*)iq, n * h->frame_samples);
+    dtl_frame_meta* d_meta = meta_out ? sg.out(SL_HMETA, meta_out, n) : sg.scratch<dtl_frame_meta>(SL_HMETA, n);
+    float2* d_taps = sg.scratch<float2>(SL_HTAPS, n * h->N);
+    dtl_header_result* d_hres = hres ? sg.out(SL_HRES, hres, n) : nullptr;
+    dtl_frame_result* d_res = sg.out(SL_RES, res, n);
+    uint8_t* d_bytes = sg.out(SL_BYTES, bytes, (size_t)S * bytes_cap);
+    int* d_nb = sg.out(SL_NBYTES, nbytes, (size_t)S);
+    dtl_tb_result* d_tbs = sg.out(SL_TBS_OUT, tbs, (size_t)S * tb_cap);
+    int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
+    int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
+    s = rx_device(h, sg, 0, d_iq, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
     if (s != DTL_OK) return s;
     return sg.finish();
 }

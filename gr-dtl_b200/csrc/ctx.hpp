@@ -57,6 +57,18 @@ struct PlanDev {
     int fb_rcp;                  // end of the blob (the SNR recurrence's reciprocals are read by snr_tags_kernel from rcp_tab)
 };
 
+// Header branch (python/dtl/ofdm_receiver.py:100-150): channel estimator, header equaliser, header parser.
+struct HdrDev {
+    int N, H, nbits, has_fec;    // fft_len, header symbols, header bits (H * |occupied[0]|), FEC header fields present
+    int max_neg, max_pos;        // range of the even integer carrier offsets ofdm_chanest_vcvc searches
+    const float2* ref;           // [N] sync word 2, shifted layout
+    const float2* corr_v;        // [N] sync2 / sync1 on the carriers sync word 1 uses, else 0
+    const uint8_t* kind;         // [H][N] 0 unused / 1 data / 2 pilot (header symbol i: pilot-carrier set i % npc)
+    const float2* pinv;          // [H][N] 1 / pilot symbol (pilot-symbol set i % nps)
+    const uint16_t* ser;         // [nbits] i*N + bin of header bit j (ofdm_serializer_vcc order, symbols_skipped 0)
+    const float2* rot;           // [2*max_off+1] channel-state rotation exp(j 2 pi off cp/N H) after the header symbols
+};
+
 // One LDPC code (gr-fec alist + cldpc permutation) in device memory.
 struct CodeDev {
     int n, m, k, rank, edges, max_row, max_col;
@@ -82,6 +94,7 @@ struct StreamState {
     int carry_len;               // LLRs of the TB in flight held in the carry buffer
     int buf_idx;                 // tb_decoder's d_buf_idx (capacity check only)
     int frame_index;             // frames seen by the FEC decoder
+    int hdr_cnst;                // header parser's fallback constellation (ofdm_adaptive_packet_header.cc:70,287-289)
 };
 
 struct TbSeg { int src; int start; int len; };   // src: -1 = carry buffer, else frame index in this call

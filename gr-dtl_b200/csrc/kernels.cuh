@@ -78,6 +78,15 @@ struct LdpcParams {                                // stand-alone fec_dec::decod
     int* cursor; int warp_bytes; int tab_bytes;
 };
 
+// ---- header branch ----------------------------------------------------------------------------------------------
+struct HdrParams {
+    HdrDev hd; PlanDev pl; CnstDev cn;
+    const float2* hfreq;                           // [n_frames][2+H][N] frequency-domain sync + header symbols
+    long long n_frames; int n_streams, F;
+    dtl_frame_meta* meta; float2* taps; dtl_header_result* hres;
+    StreamState* st;
+};
+
 struct DemapParams {
     CnstDev cn; const float2* syms; int stride_syms; const dtl_frame_meta* meta; const double* noise;
     long long n_frames; float* llr; int llr_stride; uint8_t* chunks; const uint8_t* in_chunks; float2* out_syms; int mode;
@@ -95,6 +104,7 @@ size_t ldpc_warp_bytes(int n, int slots);
 size_t ldpc_tab_bytes(int n, int m, int slots, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
 cudaError_t launch_ldpc_encode(cudaStream_t st, const CodeDev& code, const uint8_t* data, long long count, uint8_t* wire);
+cudaError_t launch_header(cudaStream_t st, const HdrParams& p);      // header_kernel + header_fix_kernel
 cudaError_t launch_demap(cudaStream_t st, const DemapParams& p);   // mode 0 soft, 1 hard, 2 map
 cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int bytes_stride, const int* fn, int n_streams, int F,
                                 uint8_t* out, int cap, int* out_n, int* err);

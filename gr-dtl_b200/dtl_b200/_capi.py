@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libdtl_b200.so")
 OK, ERR_INVALID_ARG, ERR_MISSING_TAG, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_CAPACITY, ERR_IO = range(8)
 MEM_HOST, MEM_DEVICE = 0, 1
 LDPC_REFERENCE, LDPC_LAYERED = 0, 1
-STAGES = ("fft", "eq_demap", "stream_state", "tb_plan", "ldpc", "tb_finish", "tx", "demap")
+STAGES = ("fft", "eq_demap", "stream_state", "tb_plan", "ldpc", "tb_finish", "tx", "demap", "header")
 
 frame_meta_dtype = np.dtype([
     ("constellation", "<i4"), ("carrier_offset", "<i4"), ("frame_no", "<i4"), ("payload_len", "<i4"),
@@ -26,6 +26,7 @@ frame_result_dtype = np.dtype([
     ("lost_frames", "<i4")])
 tb_result_dtype = np.dtype([("tb_no", "<i4"), ("crc_ok", "<i4"), ("nbytes", "<i4"), ("avg_it", "<i4"),
                             ("frame_index", "<i4")])
+header_result_dtype = np.dtype([("crc_ok", "<i4"), ("feedback_cnst", "<i4"), ("feedback_fec", "<i4"), ("reserved", "<i4")])
 
 _i32p, _f32p, _f64p = C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double)
 
@@ -54,7 +55,7 @@ SYMBOLS = (
     "dtl_b200_profile", "dtl_b200_stage_times",
     "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize",
     "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode",
-    "dtl_b200_rx", "dtl_b200_tx")
+    "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq")
 
 _lib = None
 
@@ -106,5 +107,7 @@ def lib():
         L.dtl_b200_ldpc_encode.argtypes = [vp, i32, vp, i64, vp, C.c_int]
         L.dtl_b200_rx.argtypes = [vp, C.c_int, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         L.dtl_b200_tx.argtypes = [vp, vp, vp, vp, i64, vp, C.c_int]
+        L.dtl_b200_rx_headers.argtypes = [vp, vp, i32, i32, vp, vp, vp, C.c_int]
+        L.dtl_b200_rx_iq.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         _lib = L
     return _lib

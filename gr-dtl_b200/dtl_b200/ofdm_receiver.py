@@ -324,6 +324,40 @@ class ofdm_receiver:
         self._ck(self._lib.dtl_b200_ldpc_encode(self._h, fec_id, a.ptr, count, _Arg(out).ptr, a.mem))
         return out
 
+    # ---- header branch (python/dtl/ofdm_receiver.py:100-150) ----------------------------------------------------
+    def rx_headers(self, iq, n_streams, frames_per_stream):
+        """chanest + header equaliser + header parser: the stream tags of every frame from its IQ alone.
+        Returns meta [S*F], taps [S*F, N] (as the payload equaliser receives them) and hres [S*F]."""
+        from ._capi import header_result_dtype
+        S, F = int(n_streams), int(frames_per_stream)
+        a = _Arg(iq)
+        o = dict(meta=self._new(a.mem, (S * F,), frame_meta_dtype), taps=self._new(a.mem, (S * F, self.fft_len), np.complex64),
+                 hres=self._new(a.mem, (S * F,), header_result_dtype))
+        self._ck(self._lib.dtl_b200_rx_headers(self._h, a.ptr, S, F, _Arg(o["meta"]).ptr, _Arg(o["taps"]).ptr,
+                                               _Arg(o["hres"]).ptr, a.mem))
+        return o
+
+    def rx_iq(self, iq, n_streams, frames_per_stream, out=None, bytes_cap=None, tb_cap=None):
+        """The receive path from IQ alone: header branch, then the payload branch on the tags it produced."""
+        from ._capi import header_result_dtype
+        S, F = int(n_streams), int(frames_per_stream)
+        a = _Arg(iq)
+        mem = a.mem
+        if out is None:
+            bytes_cap = bytes_cap or (self.bytes_stride + 8) * (F + 1)
+            tb_cap = tb_cap or 2 * F + 1
+            out = dict(res=self._new(mem, (S * F,), frame_result_dtype), bytes=self._new(mem, (S, bytes_cap), np.uint8),
+                       nbytes=self._new(mem, (S,), np.int32), tbs=self._new(mem, (S, tb_cap), tb_result_dtype),
+                       ntbs=self._new(mem, (S,), np.int32), frame_crc=self._new(mem, (S * F,), np.int32),
+                       meta=self._new(mem, (S * F,), frame_meta_dtype), hres=self._new(mem, (S * F,), header_result_dtype))
+        o = out
+        bytes_cap = o["bytes"].shape[1]
+        tb_cap = o["tbs"].shape[1] if not _is_torch(o["tbs"]) else o["tbs"].numel() // (S * tb_result_dtype.itemsize)
+        g = lambda k: _Arg(o.get(k)).ptr
+        self._ck(self._lib.dtl_b200_rx_iq(self._h, a.ptr, S, F, g("meta"), g("hres"), g("res"), g("bytes"), bytes_cap,
+                                          g("nbytes"), g("tbs"), tb_cap, g("ntbs"), g("frame_crc"), mem))
+        return o
+
     # ---- the whole payload branch ------------------------------------------------------------------------------
     def rx(self, inp, taps, meta, n_streams, frames_per_stream, freq_domain=False, out=None, bytes_cap=None, tb_cap=None):
         """IQ (or frequency-domain symbols) -> decoded payload bytes per stream.  `out` may carry preallocated

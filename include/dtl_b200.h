@@ -147,7 +147,7 @@ uint64_t dtl_b200_launch_count(const dtl_b200* h);
  * stream; dtl_b200_stage_times waits for the stream and returns, per stage, the accumulated milliseconds and
  * the number of kernel launches since the last reset (ms / launches may be NULL; n <= DTL_STAGE_COUNT). */
 enum { DTL_STAGE_FFT = 0, DTL_STAGE_EQ = 1, DTL_STAGE_STATE = 2, DTL_STAGE_TBPLAN = 3, DTL_STAGE_LDPC = 4,
-       DTL_STAGE_TBFINISH = 5, DTL_STAGE_TX = 6, DTL_STAGE_DEMAP = 7, DTL_STAGE_COUNT = 8 };
+       DTL_STAGE_TBFINISH = 5, DTL_STAGE_TX = 6, DTL_STAGE_DEMAP = 7, DTL_STAGE_HEADER = 8, DTL_STAGE_COUNT = 9 };
 dtl_status dtl_b200_profile(dtl_b200* h, int enable);
 dtl_status dtl_b200_stage_times(dtl_b200* h, double* ms, int64_t* launches, int32_t n, int reset);
 /* Page-locked host memory for DTL_MEM_HOST buffers (what a GNU Radio custom buffer would hand to work()):
@@ -238,6 +238,36 @@ dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* t
  *   iq c64 [n_frames][frame_samples] */
 dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const uint8_t* chunks, const dtl_frame_meta* meta,
                        int64_t n_frames, float* iq, int mem);
+
+/* ---- header branch: the tags of a frame from its IQ alone ------------------------
+ * python/dtl/ofdm_receiver.py:100-150: fft_vcc on the two sync symbols and the header symbols,
+ * digital.ofdm_chanest_vcvc(sync_word1, sync_word2, header_len) (integer carrier offset + channel taps),
+ * digital.ofdm_frame_equalizer_vcvc around dtl.ofdm_adaptive_header_equalizer (BPSK, symbols_skipped 0, alpha 0.1,
+ * propagate_channel_state: lib/dtl/ofdm_adaptive_equalizer.cc:161-174 -> frame_equalize :217-268),
+ * digital.ofdm_serializer_vcc, constellation_decoder_cb(BPSK) and packet_headerparser_b on
+ * ofdm_adaptive_packet_header::header_parser (lib/dtl/ofdm_adaptive_packet_header.cc:232-312).
+ *   iq    c64 [S*F][frame_samples] (in)
+ *   meta      [S*F] (out): the stream tags the payload branch receives; a header whose CRC-16 fails is dropped by
+ *             header_payload_demux: meta.reserved = 1, every other field but carrier_offset 0
+ *   taps  c64 [S*F][fft_len] (out): "ofdm_sync_chan_taps" as the payload equaliser receives it (the header equaliser's
+ *             channel state after the header symbols)
+ *   hres      [S*F] (out, nullable): header CRC flag and the feedback fields the peer wrote into the header
+ * The parser's fallback constellation (ofdm_adaptive_packet_header.cc:70,287-289) is per-stream state (dtl_b200_reset). */
+typedef struct dtl_header_result {
+    int32_t crc_ok;          /* 1: header parsed; 0: CRC-16 mismatch, frame dropped */
+    int32_t feedback_cnst;   /* "feedback_constellation_key" */
+    int32_t feedback_fec;    /* "fec_feedback_key" */
+    int32_t reserved;
+} dtl_header_result;
+dtl_status dtl_b200_rx_headers(dtl_b200* h, const float* iq, int32_t n_streams, int32_t frames_per_stream,
+                               dtl_frame_meta* meta, float* taps, dtl_header_result* hres, int mem);
+
+/* Header branch + dtl_b200_rx(in_kind 0) back to back: the receive path from IQ alone.  Dropped frames (header CRC)
+ * take no part in the payload branch (no tags, no counters, no bytes), as in the flowgraph.  meta_out / hres nullable. */
+dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_streams, int32_t frames_per_stream,
+                          dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
+                          uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                          dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem);
 
 #ifdef __cplusplus
 }

@@ -326,6 +326,17 @@ class Config:
                     bytes=[by[s, :nby[s]].copy() for s in range(S)],
                     tbs=[tbs[s, :ntbs[s]].copy() for s in range(S)], frame_crc=fcrc, seconds=secs)
 
+    def rx_headers(self, iq, S, F, nthreads=8):
+        """Header branch of the receiver (oracle/src/header.cc): the tags the payload branch receives, from IQ alone."""
+        iq = _c64_as_f32(iq)
+        meta = np.zeros(S * F, dtype=frame_meta_dtype)
+        taps = np.zeros((S * F, self.fft_len), dtype=np.complex64)
+        ok = np.zeros(S * F, dtype=np.int32)
+        fb = np.zeros((S * F, 2), dtype=np.int32)
+        if lib().orc_rx_headers(self.h, _p(iq), S, F, nthreads, _p(meta), _p(taps), _p(ok), _p(fb)) != 0:
+            raise RuntimeError("orc_rx_headers failed (sync words not configured)")
+        return dict(meta=meta, taps=taps, ok=ok, fb=fb)
+
     def rx_demod(self, iq):
         iq = _c64_as_f32(iq).reshape(-1, self.frame_samples)
         out = np.zeros((iq.shape[0], self.frame_len * self.fft_len), dtype=np.complex64)

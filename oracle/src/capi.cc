@@ -337,6 +337,12 @@ double orc_rx_batch(void* cfgh, int in_kind, const float* in, const float* taps,
             for (int j = 0; j < F; j++) {
                 size_t f = (size_t)s * F + j;
                 const cf32* tp = taps ? (const cf32*)taps + f * N : nullptr;
+                if (meta[f].reserved & 1) {        // header CRC failed: header_payload_demux emits no payload for this frame
+                    if (res) { memset(&res[f], 0, sizeof res[f]); res[f].lost_frames = (int32_t)rx.feq.lost_frames; }
+                    if (n_llr) n_llr[f] = 0;
+                    if (frame_crc) frame_crc[f] = -1;
+                    continue;
+                }
                 if (in_kind == 0) rx.frame((const cf32*)in + f * fs, tp, meta[f], &o);
                 else rx.frame_freq((const cf32*)in + f * (size_t)L * N, tp, meta[f], &o);
                 if (res) res[f] = o.res;
@@ -360,6 +366,32 @@ double orc_rx_batch(void* cfgh, int in_kind, const float* in, const float* taps,
 }
 
 // CP strip + FFT only (stage 1) for `count` frames: in [count][frame_samples] -> out [count][L][N]
+// header branch for S streams x F frames of IQ (header.cc): meta/taps as the payload branch receives them, ok[f] = header
+// CRC passed, fb[f][2] = feedback fields the peer put in the header
+int orc_rx_headers(void* cfgh, const float* iq, int S, int F, int nthreads, frame_meta* meta, float* taps, int* ok, int* fb)
+{
+    const stream_cfg& cfg = ((cfg_box*)cfgh)->c;
+    if (cfg.sync_word1.empty() || cfg.sync_word2.empty()) return -1;
+    const int N = cfg.ofdm.fft_len, fs = cfg.frame_samples();
+    if (nthreads < 1) nthreads = 1;
+    auto worker = [&](int t) {
+        for (int s = t; s < S; s += nthreads) {
+            rx_header rh(cfg);
+            for (int j = 0; j < F; j++) {
+                const size_t f = (size_t)s * F + j;
+                int fc = 0, ff = 0;
+                const bool good = rh.frame((const cf32*)iq + f * fs, &meta[f], taps ? (cf32*)taps + f * N : nullptr, &fc, &ff);
+                if (ok) ok[f] = good ? 1 : 0;
+                if (fb) { fb[2 * f] = fc; fb[2 * f + 1] = ff; }
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) th.emplace_back(worker, t);
+    for (auto& t : th) t.join();
+    return 0;
+}
+
 void orc_rx_demod(void* cfgh, const float* iq, int count, float* out)
 {
     const stream_cfg& cfg = ((cfg_box*)cfgh)->c;

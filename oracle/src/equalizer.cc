@@ -2,6 +2,7 @@
 // Restates lib/dtl/ofdm_adaptive_equalizer.cc:177-287 (ofdm_adaptive_equalizer_base),
 // lib/dtl/ofdm_adaptive_frame_equalizer_vcvc_impl.cc:99-255 (work()), the gr-digital base
 // class ofdm_equalizer_1d_pilots (RECALLED, Appendix A.3) and ofdm_serializer_vcc (A.10).
+#include "contract.hpp"
 #include "oracle.hpp"
 #include <cmath>
 #include <cstring>
@@ -9,30 +10,6 @@
 
 namespace orc {
 
-// ---- arithmetic contract (bit-exact target for the CUDA kernel) -------------------------
-static inline cf32 c_div(cf32 y, cf32 h)
-{
-    const float yr = y.real(), yi = y.imag(), hr = h.real(), hi = h.imag();
-    const float den = fmaf(hr, hr, hi * hi);
-    const float r = 1.0f / den;
-    const float nr = fmaf(yr, hr, yi * hi);
-    const float ni = fmaf(yi, hr, -(yr * hi));
-    return cf32(nr * r, ni * r);
-}
-static inline cf32 c_mul(cf32 a, cf32 b)
-{
-    const float ar = a.real(), ai = a.imag(), br = b.real(), bi = b.imag();
-    return cf32(fmaf(ar, br, -(ai * bi)), fmaf(ar, bi, ai * br));
-}
-static inline cf32 c_axpy(float alpha, cf32 h, cf32 u)   // alpha*h + u
-{
-    return cf32(fmaf(alpha, h.real(), u.real()), fmaf(alpha, h.imag(), u.imag()));
-}
-static inline cf32 expj_contract(double phase)
-{
-    const float p32 = (float)phase;                 // gr_expj takes a float
-    return cf32((float)std::cos((double)p32), (float)std::sin((double)p32));
-}
 
 // ---- ofdm_equalizer_1d_pilots ctor (RECALLED) + equalizer.cc:177-214 ---------------------
 equalizer::equalizer(const ofdm_cfg& c) : cfg(c)

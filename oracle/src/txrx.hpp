@@ -43,6 +43,23 @@ struct tx_framer {
 void map_chunks(int cnst, const uint8_t* chunks, int n, cf32* out);
 void tx_modulate(const stream_cfg& cfg, const cf32* hdr_syms, const cf32* payload_syms, cf32* iq_out);
 
+// gr-digital ofdm_chanest_vcvc (RECALLED; header.cc)
+struct chanest {
+    int N, n_data_symbols, first_active, last_active, max_neg, max_pos;
+    std::vector<cf32> ref, corr_v;                 // sync word 2; sync2/sync1 on the carriers sync word 1 uses
+    chanest(const std::vector<cf32>& sync1, const std::vector<cf32>& sync2, int n_data);
+    int carr_offset(const cf32* y1, const cf32* y2) const;
+    void chan_taps(const cf32* y2, int off, cf32* taps) const;
+};
+
+// header branch of the receiver (python/dtl/ofdm_receiver.py:100-150; header.cc): one instance per stream
+struct rx_header {
+    stream_cfg cfg; chanest est; frame_equalizer feq; packet_header parser;
+    explicit rx_header(const stream_cfg& c);
+    // iq: one frame; fills the tags the payload branch receives.  false: header CRC failed (frame dropped, m->reserved = 1)
+    bool frame(const cf32* iq, frame_meta* m, cf32* taps_out, int* fb_cnst, int* fb_fec);
+};
+
 struct rx_frame_out {
     frame_result res; const cf32* hard = nullptr; const cf32* soft = nullptr;
     const float* llr = nullptr; int n_llr = 0; int crc_ok = -1;
