@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--ref-streams", type=int, default=64, help="streams of the CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-from-iq", action="store_true")
     return ap.parse_args()
 
 
@@ -319,6 +320,42 @@ def run_b200(a):
                "decoded_mbit_per_s": bits_all / (ms_e2e * 1e-3) / 1e6,
                "api": "dtl_b200_rx(mem=DTL_MEM_HOST) via dtl_b200.ofdm_receiver.rx, page-locked host buffers"}
 
+    # ---- the receive path from IQ alone (header branch: channel estimation + header parsing on the GPU, then the same
+    # payload branch on the tags it produced); device-resident, same clock as `value`
+    from_iq = None
+    if not a.no_from_iq:
+        out2 = new_out(lambda shape, dt: rx._new(dtl_b200.MEM_DEVICE, shape, np.dtype(dt)))
+        out2["meta"] = rx._new(dtl_b200.MEM_DEVICE, (S * F,), dtl_b200.frame_meta_dtype)
+        out2["hres"] = rx._new(dtl_b200.MEM_DEVICE, (S * F,), dtl_b200.header_result_dtype)
+
+        def step_iq():
+            rx.reset(S)
+            rx.rx_iq(iq, S, F, out=out2)
+
+        for _ in range(3):
+            step_iq()
+        rx.sync()
+        hdr_ok = int(out2["hres"].cpu().numpy().view(dtl_b200.header_result_dtype)["crc_ok"].sum())
+        nby2 = out2["nbytes"].cpu().numpy()
+        rx.stage_times(reset=True)
+        rx.profile(True)
+        e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e2.record(stream)
+        for _ in range(a.steps):
+            step_iq()
+        e3.record(stream)
+        rx.sync()
+        barrier()
+        ms_iq = reduce(e2.elapsed_time(e3), "MAX") / a.steps
+        hdr_ms = rx.stage_times(reset=True)["header"][0] / a.steps
+        rx.profile(False)
+        from_iq = {"value": samples_all / (ms_iq * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_iq,
+                   "header_branch_ms_per_step": hdr_ms, "headers_parsed": hdr_ok, "frames": S * F,
+                   "decoded_mbit_per_s": reduce(float(nby2.sum()) * 8.0, "SUM") / (ms_iq * 1e-3) / 1e6,
+                   "api": "dtl_b200_rx_iq(mem=DTL_MEM_DEVICE): tags and channel taps come from the frames' own sync words and "
+                          "headers instead of the caller"}
+
     if rank != 0:
         rx.close()
         if dist is not None:
@@ -359,7 +396,7 @@ def run_b200(a):
         "config": {"workload": workload_name(a, S), "ldpc_mode": a.ldpc_mode, "l2": "inputs larger than L2 (%.0f MB IQ + "
                    "%.0f MB LLR scratch per step vs 126 MB L2)" % (iq.numel() * 8 / 1e6, frames * rx.llr_stride * 4 / 1e6),
                    "tbs_per_step_per_gpu": n_tbs, "crc_ok_tbs": crc_ok, "verified": "decoded bytes == transmitted payload"},
-        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stage_tab,
+        "e2e": e2e, "rx_from_iq": from_iq, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stage_tab,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)

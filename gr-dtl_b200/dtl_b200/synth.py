@@ -130,6 +130,51 @@ def _bits_to_chunks(bits, bps):
     return (b * w).sum(axis=-1).astype(np.uint8)
 
 
+def format_headers(meta, nbits, has_fec, feedback_cnst=0, feedback_fec=0):
+    """ofdm_adaptive_packet_header::header_formatter (lib/dtl/ofdm_adaptive_packet_header.cc:141-200, no scrambling)
+    for an array of frames: payload length 12 bits, frame number 12, constellation 4, feedback constellation 4,
+    [TB number 12, FEC feedback 4, TB offset 12, FEC id 4, TB payload 16,] CRC-16 -- every field LSB first, one bit
+    per item.  The CRC (0x1021, init 0xFFFF, output reflected) runs over the bits packed MSB first the way
+    pack_crc does (:99-111, including its `i*len + j < header_len` bound)."""
+    n = meta.shape[0]
+    bits = np.zeros((n, nbits), dtype=np.uint8)
+    k = 0
+
+    def put(val, nb):
+        nonlocal k
+        v = np.asarray(val, dtype=np.int64)
+        for i in range(nb):
+            if k < nbits:
+                bits[:, k] = (v >> i) & 1
+            k += 1
+
+    put(meta["payload_len"] & 0xFFF, 12)
+    put(meta["frame_no"] & 0xFFF, 12)
+    put(meta["constellation"] & 0xF, 4)
+    put(np.full(n, feedback_cnst & 0xF), 4)
+    if has_fec:
+        put(meta["tb_no"], 12)
+        put(np.full(n, feedback_fec), 4)
+        put(meta["tb_offset"], 12)
+        put(meta["fec_id"], 4)
+        put(meta["tb_payload"], 16)
+    ln = (nbits - 16) // 8 + (1 if (nbits - 16) % 8 else 0)
+    crc = np.full(n, 0xFFFF, dtype=np.int64)
+    for i in range(ln):
+        byte = np.zeros(n, dtype=np.int64)
+        for j in range(8):
+            if i * ln + j < nbits:
+                byte = ((byte << 1) | bits[:, i * 8 + j]) & 0xFF
+        crc ^= byte << 8
+        for _ in range(8):
+            crc = np.where(crc & 0x8000, (crc << 1) ^ 0x1021, crc << 1) & 0xFFFF
+    refl = np.zeros(n, dtype=np.int64)
+    for i in range(16):
+        refl |= ((crc >> i) & 1) << (15 - i)
+    put(refl, 16)
+    return bits
+
+
 def make_frames(rx, S, F, cnst, fec_id=0, seed=1):
     """Frames of S streams x F frames: dict(chunks u8 [S*F, cap], meta [S*F], hdr_bits u8 [S*F, H*D],
     payload = list of S byte arrays (user bytes of every TB / frame completed inside the F frames))."""
@@ -181,7 +226,7 @@ def make_frames(rx, S, F, cnst, fec_id=0, seed=1):
         d3 = data.reshape(S, T, pm)
         payload = [d3[s, done].reshape(-1) for s in range(S)]
         tb_bytes, n_done = pm, len(done)
-    hdr = rng.integers(0, 2, size=(S * F, rx.header_len * len(rx.config.occupied_carriers[0])), dtype=np.uint8)
+    hdr = format_headers(meta.reshape(S * F), rx.header_len * len(rx.config.occupied_carriers[0]), bool(fec_id))
     return dict(chunks=chunks.reshape(S * F, cap), meta=meta.reshape(S * F), hdr_bits=hdr, payload=payload,
                 tb_bytes=tb_bytes, n_done=n_done)
 
