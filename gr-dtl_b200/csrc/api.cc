@@ -312,6 +312,28 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         for (int off = -pl.max_off; off <= pl.max_off; off++) hrot[(size_t)(off + pl.max_off)] = expj_contract((2.0 * M_PI) * off * h->cp / N * H);
         hd.ref = h->d_sync2; hd.corr_v = h->upload(corr, e); hd.kind = h->upload(hkind, e); hd.pinv = h->upload(hpinv, e);
         hd.ser = h->upload(hser, e); hd.rot = h->upload(hrot, e);
+        // CRC-16 of the parser (ofdm_adaptive_packet_header.cc:99-111 pack_crc with its `i*len + j < header_len` bound, then
+        // crc(16, 0x1021, 0xFFFF, 0, false, true)) as an affine map of the header bits: crc0 ^ XOR of crc_tab[j] over set bits
+        {
+            const int nb = hd.nbits, len = nb > 16 ? (nb - 16 + 7) / 8 : 0;
+            auto crc_of = [&](int set_bit) {
+                unsigned crc = 0xFFFFu;
+                for (int i = 0; i < len; i++) {
+                    unsigned byte = 0;
+                    for (int j = 0; j < 8 && i * len + j < nb; j++) byte = ((byte << 1) | (unsigned)(i * 8 + j == set_bit)) & 0xffu;
+                    crc ^= byte << 8;
+                    for (int b = 0; b < 8; b++) crc = ((crc & 0x8000u) ? ((crc << 1) ^ 0x1021u) : (crc << 1)) & 0xFFFFu;
+                }
+                unsigned calc = 0;
+                for (int i = 0; i < 16; i++) if ((crc >> i) & 1u) calc |= 1u << (15 - i);
+                return calc;
+            };
+            hd.crc_bits = std::min(len * 8, nb);
+            hd.crc0 = crc_of(-1);
+            std::vector<uint16_t> tab((size_t)std::max(hd.crc_bits, 1), 0);
+            for (int j = 0; j < hd.crc_bits; j++) tab[(size_t)j] = (uint16_t)(crc_of(j) ^ hd.crc0);
+            hd.crc_tab = h->upload(tab, e);
+        }
         h->have_hdr = (size_t)H * N <= 65535;
     }
 
