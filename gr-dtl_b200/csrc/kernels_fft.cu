@@ -93,6 +93,83 @@ __global__ void __launch_bounds__(256) fft_fwd_kernel(const float2* __restrict__
     }
 }
 
+// ---- N = 64 (the reference's fft_len): 8 x 8 decomposition, 8 lanes per symbol, 8 points per lane ----------------------
+// n = n0 + 8 n1, k = ka + 8 kb:  X[ka + 8 kb] = sum_n0 W8^(n0 kb) . W64^(n0 ka) . sum_n1 x[n0 + 8 n1] W8^(n1 ka).
+// Lane n0 does the inner 8-point DFT in registers on global loads 64 bytes apart, applies W64^(n0 ka), and the 8 lanes of the
+// symbol transpose through shared memory ONCE (one store + one load per point, __syncwarp only: a symbol never leaves
+// its warp); lane ka then does the outer 8-point DFT and stores X[ka + 8 kb] -- 64 contiguous bytes per symbol and
+// instruction on both sides.  No CTA barrier, no staging of input or output, twiddles live in registers across the
+// grid-stride loop.
+__device__ __forceinline__ void dft8_fwd(float2 (&x)[8])
+{
+    const float r = 0.70710678118654752440f;
+#define DTL_ADD(a, b) make_float2((a).x + (b).x, (a).y + (b).y)
+#define DTL_SUB(a, b) make_float2((a).x - (b).x, (a).y - (b).y)
+    const float2 a0 = DTL_ADD(x[0], x[4]), a1 = DTL_ADD(x[1], x[5]), a2 = DTL_ADD(x[2], x[6]), a3 = DTL_ADD(x[3], x[7]);
+    const float2 b0 = DTL_SUB(x[0], x[4]), t1 = DTL_SUB(x[1], x[5]), t2 = DTL_SUB(x[2], x[6]), t3 = DTL_SUB(x[3], x[7]);
+    const float2 b1 = make_float2((t1.x + t1.y) * r, (t1.y - t1.x) * r);        // * W8^1 = (1 - i)/sqrt 2
+    const float2 b2 = make_float2(t2.y, -t2.x);                                 // * W8^2 = -i
+    const float2 b3 = make_float2((t3.y - t3.x) * r, -(t3.x + t3.y) * r);       // * W8^3 = (-1 - i)/sqrt 2
+    {   // 4-point DFT of a -> X0, X2, X4, X6
+        const float2 s0 = DTL_ADD(a0, a2), d0 = DTL_SUB(a0, a2), s1 = DTL_ADD(a1, a3), u = DTL_SUB(a1, a3);
+        const float2 d1 = make_float2(u.y, -u.x);
+        x[0] = DTL_ADD(s0, s1); x[2] = DTL_ADD(d0, d1); x[4] = DTL_SUB(s0, s1); x[6] = DTL_SUB(d0, d1);
+    }
+    {   // 4-point DFT of b -> X1, X3, X5, X7
+        const float2 s0 = DTL_ADD(b0, b2), d0 = DTL_SUB(b0, b2), s1 = DTL_ADD(b1, b3), u = DTL_SUB(b1, b3);
+        const float2 d1 = make_float2(u.y, -u.x);
+        x[1] = DTL_ADD(s0, s1); x[3] = DTL_ADD(d0, d1); x[5] = DTL_SUB(s0, s1); x[7] = DTL_SUB(d0, d1);
+    }
+#undef DTL_ADD
+#undef DTL_SUB
+}
+
+__global__ void __launch_bounds__(256) fft64_fwd_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                          unsigned n_sym, unsigned syms_per_frame, long long in_frame_stride,
+                                                          int in_sym0, int in_sym_stride, int in_skip,
+                                                          const float2* __restrict__ tw)
+{
+    __shared__ float2 xch[8][4 * 64];                          // per warp: 4 symbols
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int s = lane >> 3, t = lane & 7;                     // symbol within the warp, lane within the symbol
+    float2* xs = xch[w] + s * 64;
+    const int flip = (s & 1) << 3;                             // odd symbols use the other 64-byte half: no bank conflicts
+    float2 wt[8];
+#pragma unroll
+    for (int ka = 1; ka < 8; ka++) wt[ka] = __ldg(&tw[t * ka]);               // W64^(t ka)
+    const unsigned per_cta = 32, step = gridDim.x * per_cta;
+    for (unsigned q0 = blockIdx.x * per_cta; q0 < n_sym; q0 += step) {
+        const unsigned q = q0 + w * 4 + s;
+        const bool live = q < n_sym;
+        float2 x[8];
+        if (live) {
+            const unsigned fr = q / syms_per_frame, i = q - fr * syms_per_frame;
+            const float2* src = in + fr * in_frame_stride + (long long)(in_sym0 + (int)i) * in_sym_stride + in_skip;
+#pragma unroll
+            for (int r = 0; r < 8; r++) x[r] = __ldcs(&src[t + 8 * r]);
+        } else {
+#pragma unroll
+            for (int r = 0; r < 8; r++) x[r] = make_float2(0.f, 0.f);
+        }
+        dft8_fwd(x);
+#pragma unroll
+        for (int ka = 0; ka < 8; ka++) {
+            const float2 v = ka ? cmul(x[ka], wt[ka]) : x[0];
+            xs[(ka * 8 + (t ^ ka)) ^ flip] = v;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int n0 = 0; n0 < 8; n0++) x[n0] = xs[(t * 8 + (n0 ^ t)) ^ flip];
+        __syncwarp();
+        dft8_fwd(x);
+        if (live) {
+            float2* dst = out + (size_t)q * 64;
+#pragma unroll
+            for (int kb = 0; kb < 8; kb++) dst[t + 8 * (kb ^ 4)] = x[kb];       // out[(k + 32) % 64] = X[k], k = t + 8 kb
+        }
+    }
+}
+
 // Inverse shifted FFT, plain vectors (fft_vcc(N, False, (), True)): a[i] = in[(i+N/2)%N].
 __global__ void __launch_bounds__(256) fft_inv_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                         long long n_sym, int N, int log2n, const float2* __restrict__ tw)
@@ -177,6 +254,14 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
                            long long in_frame_stride, int in_sym0, int in_sym_stride, int in_skip, int N, const float2* tw)
 {
     if (n_sym <= 0) return cudaSuccess;
+    if (N == 64 && n_sym < 0x7fffffffLL && syms_per_frame > 0) {
+        static int sms = 0;
+        if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        const long long need = (n_sym + 31) / 32, cap = (long long)sms * 4 * 4;       // 4 resident CTAs per SM (59 registers), 4 waves
+        fft64_fwd_kernel<<<(unsigned)(need < cap ? need : cap), 256, 0, st>>>(in, out, (unsigned)n_sym, (unsigned)syms_per_frame,
+                                                                           in_frame_stride, in_sym0, in_sym_stride, in_skip, tw);
+        return cudaGetLastError();
+    }
     const int T = N / 4, threads = T >= 256 ? T : 256, G = threads / T;
     const long long blocks = (n_sym + G - 1) / G;
     const size_t smem = (size_t)G * 2 * N * sizeof(float2);
