@@ -271,6 +271,21 @@ __device__ __forceinline__ bool syndrome_nonzero(const CodeS& c, const uint8_t* 
     return __any_sync(0xffffffffu, bad);
 }
 
+// Same check with the row's edges unrolled and predicated (independent loads, no loop-carried branch).
+template <int RMAX>
+__device__ __forceinline__ bool syndrome_nonzero_u(const CodeS& c, const uint8_t* est, int lane)
+{
+    bool bad = false;
+    for (int r = lane; r < c.m; r += 32) {
+        const int deg = c.row_len()[r];
+        unsigned par = 0;
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) if (j < deg) par ^= est[c.row_var()[j * c.m + r]];
+        bad |= (par & 1u) != 0;
+    }
+    return __any_sync(0xffffffffu, bad);
+}
+
 // One flooding iteration, any degrees (awgn_bp::update_chks / update_vars, products in alist order).
 __device__ __forceinline__ void bp_iter_generic(const CodeS& c, const WarpBuf& w, int lane)
 {
@@ -394,7 +409,11 @@ __device__ __forceinline__ int bp_loop(const CodeS& c, const WarpBuf& w, int lan
         nit++;
         if (RMAX > 0) bp_iter_unrolled<(RMAX > 0 ? RMAX : 1), (CMAX > 0 ? CMAX : 1)>(c, w, lane);
         else bp_iter_generic(c, w, lane);
+#ifdef DTL_BPV_SYN
+        if (RMAX > 0 ? !syndrome_nonzero_u<(RMAX > 0 ? RMAX : 1)>(c, w.est, lane) : !syndrome_nonzero(c, w.est, lane)) break;
+#else
         if (!syndrome_nonzero(c, w.est, lane)) break;
+#endif
     }
     return nit;
 }
@@ -405,12 +424,33 @@ __device__ __forceinline__ int bp_reference_run(const CodeS& c, const WarpBuf& w
 {
     for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc
         const float m2 = -1 * 2 * w.rx[v];
+#ifndef DTL_BPV_NODIV
+        bool ok;
+        double q = ddiv_try((double)m2, sigma2, ok);
+        if (__builtin_expect(!ok, 0)) q = __ddiv_rn((double)m2, sigma2);
+        w.lr0[v] = exp(q);
+#else
         w.lr0[v] = exp(__ddiv_rn((double)m2, sigma2));
+#endif
     }
     __syncwarp();                                                                      // rx (aliases msg) is dead now
-    for (int v = lane; v < c.n; v += 32) {                                             // spa_initialize
-        const double lr = w.lr0[v];
-        for (int q = c.col_ptr()[v]; q < c.col_ptr()[v + 1]; q++) w.msg[c.col_edge()[q]] = lr;
+#ifndef DTL_BPV_NOINIT
+    const bool unroll_init = c.max_col <= 4;
+#else
+    const bool unroll_init = false;
+#endif
+    if (unroll_init) {                                                                 // spa_initialize, edges unrolled
+        for (int v = lane; v < c.n; v += 32) {
+            const double lr = w.lr0[v];
+            const int q0 = c.col_ptr()[v], deg = c.col_ptr()[v + 1] - q0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (j < deg) w.msg[c.col_edge()[q0 + j]] = lr;
+        }
+    } else {
+        for (int v = lane; v < c.n; v += 32) {
+            const double lr = w.lr0[v];
+            for (int q = c.col_ptr()[v]; q < c.col_ptr()[v + 1]; q++) w.msg[c.col_edge()[q]] = lr;
+        }
     }
     __syncwarp();
     // the unrolled instance that matches the code's degrees exactly (no wasted divisions)
@@ -696,7 +736,11 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 }
 
 // Pass 2, persistent: each warp pulls queued codewords from a device counter and runs the decoder proper.
-__global__ void __launch_bounds__(128, 5) ldpc_bp_kernel(FecParams p)
+#ifndef DTL_BP_WARPS
+#define DTL_BP_WARPS 4
+#define DTL_BP_MINB 5
+#endif
+__global__ void __launch_bounds__(32 * DTL_BP_WARPS, DTL_BP_MINB) ldpc_bp_kernel(FecParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ CodeS scodes[DTL_MAX_SMEM_CODES];
@@ -905,7 +949,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         ldpc_screen_kernel<<<sm_count * 8, 256, smem, st>>>(p);
     }
     {   // pass 2: belief propagation on what did not pass, persistent
-        const int warps = 4;
+        const int warps = DTL_BP_WARPS;
         const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
         if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
         static size_t attr_set = 0;

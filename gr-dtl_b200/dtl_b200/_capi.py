@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libdtl_b200.so")
+LIB_PATH = os.environ.get("DTL_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libdtl_b200.so")
 
 OK, ERR_INVALID_ARG, ERR_MISSING_TAG, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_CAPACITY, ERR_IO = range(8)
 MEM_HOST, MEM_DEVICE = 0, 1
