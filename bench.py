@@ -262,8 +262,11 @@ def run_b200(a):
     decoded_bits = float(nby.sum()) * 8.0
 
     # ---- device-resident timing: CUDA events on the library's stream --------------------------------------------
-    rx.profile(True)
-    rx.stage_times(reset=True)
+    # Two passes of the same K steps.  (1) The timed region proper, stage profiling OFF: the library then runs its small
+    # latency-bound kernels (TB planning, SNR tags, per-stream feedback state) on its side stream beside the heavy ones.
+    # (2) The same steps with stage profiling ON (everything serial on the main stream, one CUDA-event pair per stage) for
+    # the per-stage table and the roofline of the dominant HBM-bound kernel.
+    rx.profile(False)
     l0 = rx.launch_count
     sampler = ClockSampler(local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -278,6 +281,16 @@ def run_b200(a):
     clocks = sampler.result()
     ms_total = reduce(e0.elapsed_time(e1), "MAX")
     launches = rx.launch_count - l0
+    rx.profile(True)
+    rx.stage_times(reset=True)
+    e4, e5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e4.record(stream)
+    for _ in range(a.steps):
+        step()
+    e5.record(stream)
+    rx.sync()
+    barrier()
+    ms_serial = reduce(e4.elapsed_time(e5), "MAX") / a.steps
     stages = rx.stage_times(reset=True)
     rx.profile(False)
     ms_step = ms_total / a.steps
@@ -337,8 +350,6 @@ def run_b200(a):
         rx.sync()
         hdr_ok = int(out2["hres"].cpu().numpy().view(dtl_b200.header_result_dtype)["crc_ok"].sum())
         nby2 = out2["nbytes"].cpu().numpy()
-        rx.stage_times(reset=True)
-        rx.profile(True)
         e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e2.record(stream)
@@ -348,7 +359,12 @@ def run_b200(a):
         rx.sync()
         barrier()
         ms_iq = reduce(e2.elapsed_time(e3), "MAX") / a.steps
-        hdr_ms = rx.stage_times(reset=True)["header"][0] / a.steps
+        rx.stage_times(reset=True)
+        rx.profile(True)                          # the header branch on its own: a few profiled steps
+        for _ in range(3):
+            step_iq()
+        rx.sync()
+        hdr_ms = rx.stage_times(reset=True)["header"][0] / 3
         rx.profile(False)
         from_iq = {"value": samples_all / (ms_iq * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_iq,
                    "header_branch_ms_per_step": hdr_ms, "headers_parsed": hdr_ok, "frames": S * F,
@@ -371,7 +387,7 @@ def run_b200(a):
     for name, (ms, cnt) in stages.items():
         if cnt:
             per = ms / a.steps
-            row = {"ms_per_step": per, "share": per / ms_step, "launches_per_step": cnt / a.steps}
+            row = {"ms_per_step": per, "share": per / ms_serial, "launches_per_step": cnt / a.steps}
             if name in alg:
                 row["alg_bytes_per_frame"] = alg[name]
                 row["achieved_gbs"] = alg[name] * frames / (per * 1e-3) / 1e9
@@ -400,7 +416,7 @@ def run_b200(a):
         "config": {"workload": workload_name(a, S), "ldpc_mode": a.ldpc_mode, "l2": "inputs larger than L2 (%.0f MB IQ + "
                    "%.0f MB LLR scratch per step vs 126 MB L2)" % (iq.numel() * 8 / 1e6, frames * rx.llr_stride * 4 / 1e6),
                    "tbs_per_step_per_gpu": n_tbs, "crc_ok_tbs": crc_ok, "verified": "decoded bytes == transmitted payload"},
-        "e2e": e2e, "rx_from_iq": from_iq, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "stages": stage_tab,
+        "e2e": e2e, "rx_from_iq": from_iq, "gpu_launches": int(launches), "ms_per_step_serial": ms_serial, "clocks": clocks, "roofline": roofline, "stages": stage_tab,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)

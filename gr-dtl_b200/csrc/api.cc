@@ -80,6 +80,13 @@ struct dtl_b200 {
     cudaEvent_t ev_h2d[2] = { nullptr, nullptr }, ev_done[2] = { nullptr, nullptr };
     DevBuf pipe_in[2][3];
     int s_off = 0;                    // first stream of the chunk the device-level stages work on
+    // side stream: the small latency-bound kernels that nothing heavy waits for run beside the heavy ones --
+    // TB planning (needs the tags only) under FFT + equaliser, SNR tags + per-stream feedback state under the LDPC decoder.
+    // Off while stage profiling is on (the stage events sit on the main stream) and with DTL_NO_OVERLAP=1.
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr;
+    bool side_pending = false;
+    int overlap = -1;
 
     template <class T> T* upload(const std::vector<T>& v, cudaError_t& e)
     {
@@ -152,6 +159,8 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->out_stream) cudaStreamDestroy(h->out_stream);
+    if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
+    for (cudaEvent_t e : { h->ev_fork, h->ev_plan, h->ev_eq, h->ev_side }) if (e) cudaEventDestroy(e);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -623,6 +632,29 @@ extern "C" void dtl_b200_host_free(void* p) { if (p) cudaFreeHost(p); }
 // ---- staging: user pointer -> device pointer ----------------------------------------------------------------------------------
 namespace {
 
+// Side stream (see the handle): created on first use.
+bool side_on(dtl_b200* h)
+{
+    if (h->overlap < 0) {
+        const char* e = getenv("DTL_NO_OVERLAP");
+        h->overlap = (e && atoi(e)) ? 0 : 1;
+        if (h->overlap) {
+            bool ok = cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) == cudaSuccess;
+            for (cudaEvent_t* ev : { &h->ev_fork, &h->ev_plan, &h->ev_eq, &h->ev_side })
+                ok = ok && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) == cudaSuccess;
+            if (!ok) { cudaGetLastError(); h->overlap = 0; }
+        }
+    }
+    return h->overlap == 1 && !h->prof.on;
+}
+// The main stream waits for what was put on the side stream (no-op when nothing is pending).
+cudaError_t side_join(dtl_b200* h)
+{
+    if (!h->side_pending) return cudaSuccess;
+    h->side_pending = false;
+    return cudaStreamWaitEvent(h->stream, h->ev_side, 0);
+}
+
 struct Stage {
     dtl_b200* h; int mem; cudaError_t e = cudaSuccess;
     struct Out { void* user; void* dev; size_t bytes; };
@@ -655,6 +687,7 @@ struct Stage {
     dtl_status finish()
     {
         if (e != cudaSuccess) return cuda_fail(h, e, "staging");
+        if ((e = side_join(h)) != cudaSuccess) return cuda_fail(h, e, "side stream join");
         if (mem == DTL_MEM_DEVICE) return DTL_OK;
         for (auto& o : outs)
             if ((e = cudaMemcpyAsync(o.user, o.dev, o.bytes, cudaMemcpyDeviceToHost, h->stream)) != cudaSuccess) return cuda_fail(h, e, "cudaMemcpyAsync D2H");
@@ -710,25 +743,34 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.mag = sg.scratch<float>(SL_MAG, (size_t)n * (size_t)std::max(h->pl.npil_frame, 1));     // |pilot_eq| for snr_tags_kernel
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
     int eq_launches = 0;
+    const bool ov = side_on(h);
+    bool tags_due = false;
     h->prof.begin(DTL_STAGE_EQ, 1);
-    CK(launch_eq(h->stream, p, &eq_launches));
+    CK(launch_eq(h->stream, p, &eq_launches, ov ? &tags_due : nullptr));
     h->prof.end();
+    cudaStream_t ss = h->stream;
+    if (ov) {                                   // SNR tags and the per-stream feedback state: nothing on the main stream waits for them
+        CK(cudaEventRecord(h->ev_eq, h->stream));
+        CK(cudaStreamWaitEvent(h->side_stream, h->ev_eq, 0));
+        ss = h->side_stream;
+        if (tags_due) CK(launch_snr_tags(ss, p));
+    }
     StreamParams sp;
     sp.st = (StreamState*)h->st_buf.p + h->s_off; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
     sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
     sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
     h->prof.begin(DTL_STAGE_STATE, 1);
-    CK(launch_stream_state(h->stream, sp));
+    CK(launch_stream_state(ss, sp));
     h->prof.end();
+    if (ov) { CK(cudaEventRecord(h->ev_side, h->side_stream)); h->side_pending = true; }
     h->launches += eq_launches + 1;
     return DTL_OK;
 }
 
-dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, const dtl_frame_meta* meta, int S, int F,
-                   uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs)
+dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, const dtl_frame_meta* meta, int S, int F,
+                       uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs, FecParams& p)
 {
     if (h->codes.size() < 2) return fail(h, DTL_ERR_INVALID_ARG, "Misconfiguration: decoder not found!");
-    FecParams p;
     memset(&p, 0, sizeof p);
     const size_t tb_slots = 2 * (size_t)F + 1, budget = (size_t)S * ((size_t)F + 2);
     p.st = (StreamState*)h->st_buf.p + h->s_off; p.n_streams = S; p.F = F; p.meta = meta; p.llr = llr; p.llr_stride = llr_stride;
@@ -755,6 +797,15 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
     p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode; p.warp_bytes = h->warp_bytes;
     p.bytes = bytes; p.bytes_cap = bytes_cap; p.nbytes = nbytes; p.tb_out = tbs; p.tb_cap = tb_cap; p.ntbs = ntbs;
     p.crc_table = h->crc_table; p.err = h->d_err;
+    return DTL_OK;
+}
+
+dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, const dtl_frame_meta* meta, int S, int F,
+                   uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs)
+{
+    FecParams p;
+    dtl_status s = fec_prepare(h, sg, llr, llr_stride, meta, S, F, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, p);
+    if (s != DTL_OK) return s;
     int launches = 0;
     CK(launch_fec(h->stream, p, h->sm_count, &launches, &h->prof));
     h->launches += launches;
@@ -953,6 +1004,21 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
     const size_t n = (size_t)S * F, LN = (size_t)h->L * h->N;
     dtl_status s;
     const float2* d_freq = d_in;
+    const bool ov = h->fec_enabled && side_on(h);
+    FecParams fp;
+    float* d_llr = nullptr;
+    int launches = 0;
+    if (h->fec_enabled) {
+        d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+        if ((s = fec_prepare(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, fp)) != DTL_OK) return s;
+        if (ov) {                               // TB planning reads the tags only: beside the FFT and the equaliser
+            CK(cudaEventRecord(h->ev_fork, h->stream));
+            CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+            CK(launch_fec(h->side_stream, fp, h->sm_count, &launches, nullptr, 1));
+            CK(cudaEventRecord(h->ev_plan, h->side_stream));
+        }
+    }
     if (in_kind == 0) {
         float2* fq = sg.scratch<float2>(SL_FREQ, n * LN);
         if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
@@ -960,11 +1026,13 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
         d_freq = fq;
     }
     if (h->fec_enabled) {
-        float* d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
-        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
         s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
         if (s != DTL_OK) return s;
-        return dev_fec(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt);
+        if (ov) CK(cudaStreamWaitEvent(h->stream, h->ev_plan, 0));
+        CK(launch_fec(h->stream, fp, h->sm_count, &launches, &h->prof, ov ? 2 : 0));
+        h->launches += launches;
+        CK(side_join(h));
+        return DTL_OK;
     }
     uint8_t* fb = sg.scratch<uint8_t>(SL_FBYTES, n * h->bytes_stride);
     int* fnb = sg.scratch<int>(SL_FNBYTES, n);

@@ -96,10 +96,14 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
                            long long in_frame_stride, int in_sym0, int in_sym_stride, int in_skip, int N, const float2* tw);
 cudaError_t launch_fft_inv(cudaStream_t st, const float2* in, float2* out, long long n_sym, int N, const float2* tw);
 cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p);
-cudaError_t launch_eq(cudaStream_t st, const EqParams& p, int* launches = nullptr);   // *launches += kernels launched
+cudaError_t launch_eq(cudaStream_t st, const EqParams& p, int* launches = nullptr, bool* tags_deferred = nullptr);   // *launches += kernels launched
+// tags_deferred != nullptr: the lean kernel's snr_tags_kernel is left to the caller (launch_snr_tags, any stream ordered
+// after `st`), *tags_deferred says whether one is due
+cudaError_t launch_snr_tags(cudaStream_t st, const EqParams& p);
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
-cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof);
+// phase 0: everything; 1: TB planning only (needs the tags, not the LLRs); 2: what follows the planning
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase = 0);
 size_t ldpc_warp_bytes(int n, int slots);
 size_t ldpc_tab_bytes(int n, int m, int slots, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);

@@ -930,14 +930,18 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
 
 __global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; *bits_used = 0ull; }
 
-cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof)
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase)
 {
     if (p.n_streams <= 0 || p.F <= 0) return cudaSuccess;
     Prof none; if (!prof) prof = &none;
-    prof->begin(DTL_STAGE_TBPLAN, 2);
-    fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
-    tb_plan_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
-    prof->end();
+    if (phase != 2) {
+        prof->begin(DTL_STAGE_TBPLAN, 2);
+        fec_clear_kernel<<<1, 1, 0, st>>>(p.cnt, p.bits_used);
+        tb_plan_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
+        prof->end();
+        if (launches) *launches += 2;
+        if (phase == 1) return cudaGetLastError();
+    }
     {   // pass 1: screening, grid-stride over the codeword work list
         const size_t smem = (size_t)p.screen_tab_bytes + 8 * (size_t)p.screen_bytes;
         static size_t attr_set = 0;
@@ -969,7 +973,7 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     tb_gather_kernel<<<p.n_streams, 128, 0, st>>>(p);
     carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     prof->end();
-    if (launches) *launches += 7;
+    if (launches) *launches += 5;
     return cudaGetLastError();
 }
 
