@@ -39,7 +39,8 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES, SL_COUNT
+    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
+    SL_TXDATA, SL_TXLEN, SL_TXCNST, SL_TXFEC, SL_TXTBS, SL_TXNTB, SL_TXKEEP, SL_TXSEGS, SL_TXCRC, SL_TXBITS, SL_TXCHUNKS, SL_TXMETA, SL_TXCONS, SL_TXSTARTED, SL_COUNT
 };
 
 } // namespace
@@ -67,10 +68,11 @@ struct dtl_b200 {
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
     HdrDev hd{}; bool have_hdr = false;   // header branch tables (need the sync words)
-    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
+    int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, max_n = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
     // per-stream state
     int n_streams = 0;
     DevBuf st_buf, carry_buf, pend_buf;
+    DevBuf txst_buf, txcarry_buf; int tx_streams = -1;   // TX FEC framer state (allocated by its first call)
     int carry_cap = 0;
     int* d_err = nullptr; int* d_cnt = nullptr; unsigned long long* d_bits_used = nullptr; int* d_cursor = nullptr;
     int* h_err = nullptr;             // pinned mirror of d_err
@@ -150,7 +152,7 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
-    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release();
+    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->txst_buf.release(); h->txcarry_buf.release();
     h->prof.release();
     for (int i = 0; i < 2; i++) {
         if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
@@ -479,6 +481,7 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
     }
     h->d_codes = h->upload(cd, e);
     if (max_n) {
+        h->max_n = max_n;
         h->max_ncws = tb_ncws_host(max_n, h->cap * h->max_bps);       // fec_decoder_impl.cc:54-72
         h->max_tb = max_n * h->max_ncws;
         // codes with a smaller n split a frame into more codewords
@@ -557,6 +560,7 @@ extern "C" dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams)
     h->launches += n_streams > 0 ? 1 : 0;
     CK(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
     h->n_streams = n_streams;
+    h->tx_streams = -1;                          // the TX framer starts over as well (state re-created by its next call)
     return DTL_OK;
 }
 
@@ -1227,6 +1231,50 @@ extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_str
     if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
     s = rx_device(h, sg, 0, d_iq, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
     if (s != DTL_OK) return s;
+    return sg.finish();
+}
+
+// ---- TX FEC framer ---------------------------------------------------------------------------------------
+extern "C" dtl_status dtl_b200_fec_frame(dtl_b200* h, const uint8_t* data, int32_t in_cap, const int32_t* in_len,
+                                         const int32_t* cnst, const int32_t* fec_id, int32_t n_streams, int32_t frames_per_stream,
+                                         uint8_t* chunks, dtl_frame_meta* meta, int32_t* consumed, int32_t* tbs_started, int mem)
+{
+    if (!h || !data || !cnst || !fec_id || !chunks || !meta || n_streams < 0 || frames_per_stream < 0 || in_cap < 0) return DTL_ERR_INVALID_ARG;
+    if (!h->fec_enabled || h->codes.size() < 2) return fail(h, DTL_ERR_INVALID_ARG, "the FEC framer needs a FEC-enabled configuration");
+    CK(cudaSetDevice(h->device));
+    const int S = n_streams, F = frames_per_stream;
+    const size_t n = (size_t)S * F;
+    const int maxbits = (h->max_ncws * h->max_n + 15) & ~15;
+    if (h->tx_streams != S) {                    // first call (or after dtl_b200_reset): framer state starts empty
+        CK(cudaStreamSynchronize(h->stream));
+        CK(h->txst_buf.ensure(std::max<size_t>((size_t)S * sizeof(TxStream), 16)));
+        CK(h->txcarry_buf.ensure((size_t)S * maxbits + 16));
+        CK(launch_txf_reset(h->stream, (TxStream*)h->txst_buf.p, S));
+        h->tx_streams = S;
+    }
+    Stage sg(h, mem);
+    TxfParams p;
+    memset(&p, 0, sizeof p);
+    p.st = (TxStream*)h->txst_buf.p; p.n_streams = S; p.F = F; p.cap = h->cap;
+    p.data = sg.in(SL_TXDATA, data, (size_t)S * in_cap); p.in_cap = in_cap;
+    p.in_len = in_len ? sg.in(SL_TXLEN, in_len, (size_t)S) : nullptr;
+    p.cnst = sg.in(SL_TXCNST, cnst, n); p.fec = sg.in(SL_TXFEC, fec_id, n);
+    p.n_codes = (int)h->codes.size() - 1; p.codes = h->d_codes;
+    for (int c = 0; c <= DTL_CNST_MAX; c++) p.bps_tab[c] = cnst_bps(c);
+    p.tbs = sg.scratch<TxTb>(SL_TXTBS, n); p.ntb = sg.scratch<int>(SL_TXNTB, (size_t)S); p.keep = sg.scratch<int>(SL_TXKEEP, (size_t)S);
+    p.segs = sg.scratch<TxSeg>(SL_TXSEGS, 2 * n); p.tbcrc = sg.scratch<uint32_t>(SL_TXCRC, n);
+    p.tbbits = sg.scratch<uint8_t>(SL_TXBITS, n * (size_t)maxbits); p.maxbits = maxbits;
+    p.carry = (uint8_t*)h->txcarry_buf.p;
+    p.max_ncws = h->max_ncws; p.max_kwords = (h->max_k + 31) / 32;
+    p.chunks = sg.out(SL_TXCHUNKS, chunks, n * (size_t)h->cap);
+    p.meta = sg.out(SL_TXMETA, meta, n);
+    p.consumed = consumed ? sg.out(SL_TXCONS, consumed, (size_t)S) : nullptr;
+    p.tbs_started = tbs_started ? sg.out(SL_TXSTARTED, tbs_started, (size_t)S) : nullptr;
+    p.crc_table = h->crc_table; p.err = h->d_err;
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    int launches = 0;
+    CK(launch_txf(h->stream, p, &launches));
+    h->launches += launches;
     return sg.finish();
 }
 

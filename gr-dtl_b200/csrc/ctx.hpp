@@ -100,6 +100,11 @@ struct StreamState {
     int hdr_cnst;                // header parser's fallback constellation (ofdm_adaptive_packet_header.cc:70,287-289)
 };
 
+// TX FEC framer (kernels_txf.cu): per-stream state that survives between calls, and the per-call plan
+struct TxStream { int tb_count, frame_count; int rem, total; int cur_fec, cur_payload; };   // rem/total: bits of the TB in flight
+struct TxTb { int fec_id, ncws, payload_bytes, in_off, bits; };
+struct TxSeg { int tb, bit0, nbits, chunk0; };        // tb: index among this call's TBs of the stream, -1 = carry buffer
+
 struct TbSeg { int src; int start; int len; };   // src: -1 = carry buffer, else frame index in this call
 #define DTL_TB_MAXSEG 6
 struct TbDesc {

@@ -78,6 +78,23 @@ struct LdpcParams {                                // stand-alone fec_dec::decod
     int* cursor; int warp_bytes; int tab_bytes;
 };
 
+// ---- TX FEC framer --------------------------------------------------------------------------------
+struct TxfParams {
+    TxStream* st; int n_streams, F, cap;
+    const uint8_t* data; int in_cap; const int* in_len;      // [S][in_cap] user bytes, [S] valid bytes (or null: in_cap)
+    const int* cnst; const int* fec;                          // [S*F] constellation / FEC id of the frame (the MCS feedback)
+    int n_codes; const CodeDev* codes; int bps_tab[DTL_CNST_MAX + 1];
+    TxTb* tbs; int* ntb; int* keep; TxSeg* segs;              // [S][F], [S], [S], [S*F][2]
+    uint32_t* tbcrc;                                          // [S][F]
+    uint8_t* tbbits; int maxbits;                             // [S][F][maxbits] encoded TB bit streams, one bit per byte
+    uint8_t* carry;                                           // [S][maxbits] bits of the TB in flight across calls
+    int max_ncws, max_kwords;
+    uint8_t* chunks; dtl_frame_meta* meta; int* consumed; int* tbs_started;
+    const uint32_t* crc_table; int* err;
+};
+cudaError_t launch_txf(cudaStream_t st, const TxfParams& p, int* launches);
+cudaError_t launch_txf_reset(cudaStream_t st, TxStream* s, int n);
+
 // ---- header branch ----------------------------------------------------------------------------------------------
 struct HdrParams {
     HdrDev hd; PlanDev pl; CnstDev cn;

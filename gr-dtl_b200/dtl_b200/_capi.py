@@ -55,7 +55,7 @@ SYMBOLS = (
     "dtl_b200_profile", "dtl_b200_stage_times",
     "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize",
     "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode",
-    "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq")
+    "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq", "dtl_b200_fec_frame")
 
 _lib = None
 
@@ -107,6 +107,7 @@ def lib():
         L.dtl_b200_ldpc_encode.argtypes = [vp, i32, vp, i64, vp, C.c_int]
         L.dtl_b200_rx.argtypes = [vp, C.c_int, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         L.dtl_b200_tx.argtypes = [vp, vp, vp, vp, i64, vp, C.c_int]
+        L.dtl_b200_fec_frame.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, vp, vp, vp, vp, C.c_int]
         L.dtl_b200_rx_headers.argtypes = [vp, vp, i32, i32, vp, vp, vp, C.c_int]
         L.dtl_b200_rx_iq.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         _lib = L

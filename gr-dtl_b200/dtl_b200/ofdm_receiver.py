@@ -380,6 +380,22 @@ class ofdm_receiver:
         return o
 
     # ---- stage 5: chunks_to_symbols + carrier allocator + IFFT + cyclic prefixer (ofdm_transmitter.py:95-98,168-189)
+    def fec_frame(self, data, cnst, fec_id, S, F, in_len=None):
+        """TX FEC framer (dtl.ofdm_adaptive_fec_frame_bvb, lib/dtl/ofdm_adaptive_fec_frame_bvb_impl.cc:343-432): user bytes
+        u8 [S, in_cap], per-frame constellation and FEC id int32 [S*F] -> dict(chunks u8 [S*F, frame_capacity],
+        meta [S*F], consumed int32 [S], tbs_started int32 [S]).  The TB in flight continues in the next call."""
+        a_d, a_c, a_f = _Arg(data), _Arg(cnst), _Arg(fec_id)
+        a_l = _Arg(in_len) if in_len is not None else None
+        mem = _mem_of(a_d, a_c, a_f) if a_l is None else _mem_of(a_d, a_c, a_f, a_l)
+        in_cap = int(data.shape[-1]) if len(data.shape) > 1 else int(data.shape[0]) // max(S, 1)
+        out = dict(chunks=self._new(mem, (S * F, self.frame_capacity), np.uint8),
+                   meta=self._new(mem, (S * F,), _capi.frame_meta_dtype),
+                   consumed=self._new(mem, (S,), np.int32), tbs_started=self._new(mem, (S,), np.int32))
+        self._ck(self._lib.dtl_b200_fec_frame(self._h, a_d.ptr, in_cap, a_l.ptr if a_l is not None else None, a_c.ptr, a_f.ptr,
+                                              S, F, _Arg(out["chunks"]).ptr, _Arg(out["meta"]).ptr,
+                                              _Arg(out["consumed"]).ptr, _Arg(out["tbs_started"]).ptr, mem))
+        return out
+
     def tx(self, hdr_bits, chunks, meta):
         a_h, a_c, a_m = _Arg(hdr_bits), _Arg(chunks), _Arg(meta)
         mem = _mem_of(a_h, a_c, a_m)

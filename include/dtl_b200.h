@@ -239,6 +239,22 @@ dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* t
 dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const uint8_t* chunks, const dtl_frame_meta* meta,
                        int64_t n_frames, float* iq, int mem);
 
+/* ---- TX FEC framer ----------------------------------------------------------------------
+ * dtl.ofdm_adaptive_fec_frame_bvb (lib/dtl/ofdm_adaptive_fec_frame_bvb_impl.cc:343-432) with tb_encoder
+ * (lib/dtl/tb_encoder.cc:32-74,88-99), crc_util::append_crc (lib/dtl/crc_util.cc:31-39) and ldpc_enc::encode
+ * (lib/dtl/ldpc_enc.cc:58-68): user bytes -> frames of constellation chunks + the tags the header formatter and the
+ * modulator (dtl_b200_tx) consume.  S streams x F consecutive frames per call; the TB in flight at the end of the call is
+ * continued by the next call (per-stream state, cleared by dtl_b200_reset).  The reference block is paced by wall clock and
+ * by what its input holds: here a TB is started whenever the frame has room and the stream's input still holds a whole TB
+ * payload (never on less).
+ *   data  u8  [S][in_cap] (in), in_len [S] valid bytes per stream (NULL: in_cap)
+ *   cnst, fec_id [S*F] (in): constellation and 1-based FEC id of each frame (the MCS the feedback selected)
+ *   chunks u8 [S*F][frame_capacity] (out), meta [S*F] (out: constellation, frame_no, payload_len, packet_len, fec_id,
+ *   tb_no, tb_offset, tb_payload), consumed [S] (out, optional: input bytes used), tbs_started [S] (out, optional) */
+dtl_status dtl_b200_fec_frame(dtl_b200* h, const uint8_t* data, int32_t in_cap, const int32_t* in_len,
+                              const int32_t* cnst, const int32_t* fec_id, int32_t n_streams, int32_t frames_per_stream,
+                              uint8_t* chunks, dtl_frame_meta* meta, int32_t* consumed, int32_t* tbs_started, int mem);
+
 /* ---- header branch: the tags of a frame from its IQ alone ------------------------
  * python/dtl/ofdm_receiver.py:100-150: fft_vcc on the two sync symbols and the header symbols,
  * digital.ofdm_chanest_vcvc(sync_word1, sync_word2, header_len) (integer carrier offset + channel taps),

@@ -337,6 +337,28 @@ class Config:
             raise RuntimeError("orc_rx_headers failed (sync words not configured)")
         return dict(meta=meta, taps=taps, ok=ok, fb=fb)
 
+    def frame_batch(self, data, cnst, fec_id, S, F, in_len=None, state=None):
+        """TX FEC framer alone (oracle/src/txrx.cc tx_framer fed with the caller's bytes): data u8 [S, in_cap], cnst /
+        fec_id int32 [S*F] -> dict(chunks u8 [S*F, capacity], meta [S*F], consumed [S], started [S]).  `state`: a list
+        returned by an earlier call (the TB in flight continues), or None."""
+        data = np.ascontiguousarray(data, dtype=np.uint8).reshape(S, -1)
+        cnst = np.ascontiguousarray(cnst, dtype=np.int32).reshape(S * F)
+        fec_id = np.ascontiguousarray(fec_id, dtype=np.int32).reshape(S * F)
+        chunks = np.zeros((S * F, self.capacity), dtype=np.uint8)
+        meta = np.zeros(S * F, dtype=frame_meta_dtype)
+        consumed = np.zeros(S, dtype=np.int32)
+        started = np.zeros(S, dtype=np.int32)
+        st = state if state is not None else (C.c_void_p * S)()
+        il = None if in_len is None else np.ascontiguousarray(in_len, dtype=np.int32)
+        f = lib().orc_frame_batch
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        if f(self.h, S, F, _p(cnst), _p(fec_id), _p(data), data.shape[1], None if il is None else _p(il), _p(chunks), _p(meta),
+             _p(consumed), _p(started), C.cast(st, C.c_void_p)) != 0:
+            raise RuntimeError("orc_frame_batch failed")
+        return dict(chunks=chunks, meta=meta, consumed=consumed, started=started, state=st)
+
     def rx_demod(self, iq):
         iq = _c64_as_f32(iq).reshape(-1, self.frame_samples)
         out = np.zeros((iq.shape[0], self.frame_len * self.fft_len), dtype=np.complex64)

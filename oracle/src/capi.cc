@@ -245,6 +245,33 @@ int orc_hdr_parse(void* h, const uint8_t* in, frame_meta* m, int* fb_cnst, int* 
 //   taps     c64[S*F][N]             (N*h_s + estimation noise: stands in for ofdm_chanest_vcvc)
 //   payload  u8 [S][payload_cap]     user bytes of every TB/frame completed inside the F frames
 // cnst_per_frame (nullable, [S*F]) overrides `cnst`.
+// TX FEC framer alone: user bytes of each stream -> chunks + tags, F consecutive frames per stream.
+// state != nullptr: [S] opaque framer handles kept between calls (created on first use, freed by orc_frame_free).
+int orc_frame_batch(void* cfgh, int S, int F, const int* cnst_per_frame, const int* fec_per_frame, const uint8_t* data,
+                    int in_cap, const int* in_len, uint8_t* chunks, frame_meta* meta, int* consumed, int* started, void** state)
+{
+    const stream_cfg& cfg = ((cfg_box*)cfgh)->c;
+    const int cap = cfg.capacity();
+    try {
+        for (int s = 0; s < S; s++) {
+            tx_framer local(cfg, 1);
+            tx_framer* fr = &local;
+            if (state) { if (!state[s]) state[s] = new tx_framer(cfg, 1); fr = (tx_framer*)state[s]; }
+            fr->src = data + (size_t)s * in_cap; fr->src_len = in_len ? std::min(in_len[s], in_cap) : in_cap; fr->src_pos = 0;
+            const int tb0 = fr->tb_count;
+            std::vector<std::vector<uint8_t>> done;
+            for (int j = 0; j < F; j++) {
+                const size_t f = (size_t)s * F + j;
+                fr->next_frame(cnst_per_frame[f], fec_per_frame[f], chunks + f * cap, &meta[f], done);
+            }
+            if (consumed) consumed[s] = fr->src_pos;
+            if (started) started[s] = fr->tb_count - tb0;
+        }
+    } catch (const std::exception&) { return -1; }
+    return 0;
+}
+void orc_frame_free(void** state, int S) { for (int s = 0; s < S; s++) { delete (tx_framer*)state[s]; state[s] = nullptr; } }
+
 int orc_tx_batch(void* cfgh, int S, int F, uint64_t seed, int cnst, int fec_id, double snr_db, int nthreads,
                  const int* cnst_per_frame, uint8_t* chunks, frame_meta* meta, float* iq, float* taps,
                  uint8_t* payload, int payload_cap, int* payload_len, int* payload_tbs)

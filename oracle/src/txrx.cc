@@ -122,7 +122,7 @@ int stream_cfg::frame_samples() const { return (frame_len + header_syms() + 2) *
 // ---- TX framer (this repo's generator; see file header) -------------------------------------------
 tx_framer::tx_framer(const stream_cfg& c, uint64_t seed) : cfg(c), r{ seed }, crc(4, 0x04C11DB7, 0xFFFFFFFF, 0xFFFFFFFF) {}
 
-void tx_framer::new_tb(int cnst, int fec_id)
+bool tx_framer::new_tb(int cnst, int fec_id)
 {
     const ldpc_code& code = *cfg.codes[fec_id];
     const int bps = bits_per_symbol(cnst), cap = cfg.capacity();
@@ -131,7 +131,13 @@ void tx_framer::new_tb(int cnst, int fec_id)
     int payload_max = (cur_ncws * code.K) / 8 - 4;             // fec_frame_bvb_impl.cc:369-370
     if (payload_max <= 0) throw std::runtime_error("Misconfiguration: TB should be able to carry at least 1 user data bit");
     std::vector<uint8_t> bytes(payload_max + 4);
-    for (int i = 0; i < payload_max; i++) bytes[i] = (uint8_t)(r.next() & 0xff);
+    if (src) {
+        if (src_pos + payload_max > src_len) return false;
+        memcpy(bytes.data(), src + src_pos, payload_max);
+        src_pos += payload_max;
+    } else {
+        for (int i = 0; i < payload_max; i++) bytes[i] = (uint8_t)(r.next() & 0xff);
+    }
     crc.append_crc(bytes.data(), payload_max);                 // :394-399
     std::vector<uint8_t> bits((size_t)(payload_max + 4) * 8);
     repack to_bits(8, 1);
@@ -140,6 +146,7 @@ void tx_framer::new_tb(int cnst, int fec_id)
     tb_count++;
     cur_payload.assign(bytes.begin(), bytes.begin() + payload_max);
     cur_tb_fec = fec_id;
+    return true;
 }
 
 // One frame of `capacity` chunks + its tags.  TBs whose last bit went out in this frame are
@@ -177,9 +184,8 @@ void tx_framer::next_frame(int cnst, int fec_id, uint8_t* chunks, frame_meta* m,
     // (2) start the next TB at the next symbol boundary if there is room (tb_decoder.cc:112-124)
     if (enc.ready()) {
         int avail = (cap - used) * bps / 8;
-        if (avail > 0) {
+        if (avail > 0 && new_tb(cnst, fec_id)) {
             offset = payload;
-            new_tb(cnst, fec_id);
             started_new = true;
             int out_bytes = std::min(align_bits_to_bytes(enc.remaining()), avail);
             // keep ceil(payload*8/bps) (what the header parser derives, packet_header.cc:281-284)

@@ -34,10 +34,12 @@ struct tx_framer {
     stream_cfg cfg; rng r; crc_util crc; tb_encoder enc;
     int tb_count = 0, frame_count = 0, cur_ncws = 0, cur_tb_fec = 0;
     std::vector<uint8_t> cur_payload;
+    // user bytes: from `src` when set (a TB is only started while a whole TB payload is left), else pseudo-random
+    const uint8_t* src = nullptr; int src_len = 0, src_pos = 0;
     tx_framer(const stream_cfg& c, uint64_t seed);
     void next_frame(int cnst, int fec_id, uint8_t* chunks, frame_meta* m, std::vector<std::vector<uint8_t>>& done);
   private:
-    void new_tb(int cnst, int fec_id);
+    bool new_tb(int cnst, int fec_id);
 };
 
 void map_chunks(int cnst, const uint8_t* chunks, int n, cf32* out);
