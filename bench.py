@@ -372,6 +372,36 @@ def run_b200(a):
                    "api": "dtl_b200_rx_iq(mem=DTL_MEM_DEVICE): tags and channel taps come from the frames' own sync words and "
                           "headers instead of the caller"}
 
+    # ---- TX FEC framer: user bytes -> chunks + tags for the same S x F frames, device-resident
+    tx_framer = None
+    fec_id, cap = 1, rx.frame_capacity
+    if not a.no_from_iq:
+        pay = 8 * F * ((cap * bps // 8) + 64)
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(99 + rank)
+        t_data = torch.randint(0, 256, (S, pay), generator=gen, device=dev, dtype=torch.uint8)
+        t_c = torch.full((S * F,), int(a.cnst), device=dev, dtype=torch.int32)
+        t_f = torch.full((S * F,), int(fec_id), device=dev, dtype=torch.int32)
+        torch.cuda.synchronize(dev)
+        for _ in range(3):
+            rx.reset(S)
+            fo = rx.fec_frame(t_data, t_c, t_f, S, F)
+        rx.sync()
+        used = float(fo["consumed"].sum().item())
+        e6, e7 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e6.record(stream)
+        for _ in range(a.steps):
+            rx.reset(S)
+            fo = rx.fec_frame(t_data, t_c, t_f, S, F)
+        e7.record(stream)
+        rx.sync()
+        barrier()
+        ms_tx = reduce(e6.elapsed_time(e7), "MAX") / a.steps
+        tx_framer = {"ms_per_step": ms_tx, "frames": S * F, "payload_mbit_per_s": reduce(used * 8.0, "SUM") / (ms_tx * 1e-3) / 1e6,
+                     "api": "dtl_b200_fec_frame(mem=DTL_MEM_DEVICE): CRC-32, TB split, LDPC encode, chunk packing, tags"}
+        del t_data, fo
+
     if rank != 0:
         rx.close()
         if dist is not None:
@@ -416,7 +446,7 @@ def run_b200(a):
         "config": {"workload": workload_name(a, S), "ldpc_mode": a.ldpc_mode, "l2": "inputs larger than L2 (%.0f MB IQ + "
                    "%.0f MB LLR scratch per step vs 126 MB L2)" % (iq.numel() * 8 / 1e6, frames * rx.llr_stride * 4 / 1e6),
                    "tbs_per_step_per_gpu": n_tbs, "crc_ok_tbs": crc_ok, "verified": "decoded bytes == transmitted payload"},
-        "e2e": e2e, "rx_from_iq": from_iq, "gpu_launches": int(launches), "ms_per_step_serial": ms_serial, "clocks": clocks, "roofline": roofline, "stages": stage_tab,
+        "e2e": e2e, "rx_from_iq": from_iq, "tx_fec_framer": tx_framer, "gpu_launches": int(launches), "ms_per_step_serial": ms_serial, "clocks": clocks, "roofline": roofline, "stages": stage_tab,
         "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)
