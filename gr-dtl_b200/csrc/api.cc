@@ -792,7 +792,15 @@ dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride,
     p.cw_tb = sg.scratch<int>(SL_CWTB, (size_t)p.cw_cap);
     p.cw_nit = sg.scratch<int>(SL_CWNIT, (size_t)p.cw_cap);
     p.cw_geo = sg.scratch<int>(SL_CWGEO, (size_t)p.cw_cap * 3);
-    p.bp_list = sg.scratch<int>(SL_BPLIST, (size_t)p.cw_cap);
+    p.bp_list = sg.scratch<int>(SL_BPLIST, 4 * (size_t)p.cw_cap);
+    {
+        static int th[3] = { -1, 0, 0 };
+        if (th[0] < 0) {
+            th[0] = 6; th[1] = 4; th[2] = 2;
+            if (const char* e = getenv("DTL_BP_BUCKETS")) sscanf(e, "%d,%d,%d", &th[0], &th[1], &th[2]);
+        }
+        p.bp_th[0] = th[0]; p.bp_th[1] = th[1]; p.bp_th[2] = th[2];
+    }
     p.tab_bytes = h->tab_bytes; p.screen_bytes = h->screen_bytes; p.screen_tab_bytes = h->screen_tab_bytes; p.screen_words = h->screen_words;
     p.bits_cap = (long long)budget * ((long long)h->max_ncws * h->max_k + 4);
     p.bits = sg.scratch<uint8_t>(SL_BITS, (size_t)p.bits_cap + 64);

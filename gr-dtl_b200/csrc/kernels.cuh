@@ -59,12 +59,14 @@ struct FecParams {
     int* tb_count;                                 // [S]
     int* tb_list;                                  // compact list of released TB indices
     int* cw_tb; int cw_cap;                        // codeword work list: TB index of work item
-    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs, [3] queued for BP
+    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs, [3],[5],[6],[7] queued for BP
     unsigned long long* bits_used;                 // bump allocator of the bit scratch
     uint8_t* bits; long long bits_cap;             // decoded TB bits, one byte per bit, then packed in place
     int* cw_nit;                                   // [cw_cap]
     int* cw_geo;                                   // [cw_cap][3]: first LLR of the codeword in the TB, first data bit, k_
-    int* bp_list;                                  // [cw_cap] codewords that failed the initial syndrome check (cnt[3] of them)
+    int* bp_list;                                  // [4][cw_cap] codewords that failed the initial syndrome check, hardest-looking list
+                                                   // first (cnt[3], cnt[5], cnt[6], cnt[7] of them)
+    int bp_th[3];                                  // list 0: >= bp_th[0] lanes saw a failing check, list 1: >= bp_th[1], ...
     int screen_words;                              // ceil(max n / 32)
     int tab_bytes, screen_bytes, screen_tab_bytes; // shared-memory graph tables; per-warp bytes and table bytes of the screening pass
     int max_it; double sigma2; int mode; int warp_bytes;

@@ -685,6 +685,7 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
         __syncwarp();
         // ---- syndromes
         unsigned badw = 0;
+        int heavy = 32;
         if (uniform) {
             const ScreenCode sc = s_code[fec0];
             const int nw = (sc.n + 31) >> 5;
@@ -698,6 +699,12 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
 #pragma unroll 3
                 for (int j = 0; j < sc.max_row; j++) par ^= plane[rwr[j * sc.m]];
                 badw |= par;
+            }
+            // how hard each codeword looks: the number of lanes that saw a failing check of it (a coarse syndrome weight)
+#pragma unroll
+            for (int c = 0; c < 32; c++) {
+                const unsigned b = __ballot_sync(0xffffffffu, (badw >> c) & 1u);
+                if (lane == c) heavy = __popc(b);
             }
             badw = __reduce_or_sync(0xffffffffu, badw);
         } else {
@@ -724,12 +731,20 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
             for (int q = lane; q < k_; q += 32) { const unsigned v = rank + q; out[q] = (uint8_t)((row[v >> 5] >> (v & 31u)) & 1u); }
         }
         if (lane < cnt && !((badw >> lane) & 1u)) p.cw_nit[it0 + lane] = 0;
-        const int n_bad = __popc(badw);
-        if (n_bad) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&p.cnt[3], n_bad);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if ((badw >> lane) & 1u) p.bp_list[base + __popc(badw & ((1u << lane) - 1u))] = it0 + lane;
+        // four lists, hardest-looking first: the decoder takes them in that order, so the codewords that run all
+        // max_it iterations start early and the short ones fill the end of the launch
+        if (badw) {
+            const bool mine = (badw >> lane) & 1u;
+            const int bucket = heavy >= p.bp_th[0] ? 0 : heavy >= p.bp_th[1] ? 1 : heavy >= p.bp_th[2] ? 2 : 3;
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const unsigned mk = __ballot_sync(0xffffffffu, mine && bucket == b);
+                if (!mk) continue;
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&p.cnt[b == 0 ? 3 : 4 + b], __popc(mk));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if ((mk >> lane) & 1u) p.bp_list[(size_t)b * p.cw_cap + base + __popc(mk & ((1u << lane) - 1u))] = it0 + lane;
+            }
         }
         __syncwarp();
     }
@@ -747,13 +762,14 @@ __global__ void __launch_bounds__(32 * DTL_BP_WARPS, DTL_BP_MINB) ldpc_bp_kernel
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     DTL_STAGE_ALL_CODES(p, scodes, sm)
     unsigned char* base = sm + p.tab_bytes + (size_t)wid * p.warp_bytes;
-    const int total = p.cnt[3];
+    const int n0 = p.cnt[3], n1 = n0 + p.cnt[5], n2 = n1 + p.cnt[6], total = n2 + p.cnt[7];
     for (;;) {
         int j = 0;
         if (lane == 0) j = atomicAdd(&p.cnt[1], 1);
         j = __shfl_sync(0xffffffffu, j, 0);
         if (j >= total) break;
-        const int it = p.bp_list[j];
+        const int it = j < n0 ? p.bp_list[j] : j < n1 ? p.bp_list[(size_t)p.cw_cap + (j - n0)]
+                     : j < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (j - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (j - n2)];
         const TbDesc& d = p.tbs[p.cw_tb[it]];
         CodeS c = scodes[d.fec_id];
         c.smb = sm;
@@ -928,7 +944,11 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
     }
 }
 
-__global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used) { cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; *bits_used = 0ull; }
+__global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used)
+{
+    cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; cnt[5] = cnt[6] = cnt[7] = 0;     // cnt[4] is the stand-alone decoder's cursor
+    *bits_used = 0ull;
+}
 
 cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase)
 {
