@@ -438,7 +438,8 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         // slot-major edge storage: edge j of row r (mlist order) is slot j*m + r (kernels_fec.cu)
         const int slots = code.max_row * code.m;
         if (slots > 65535) return fail(h, DTL_ERR_UNSUPPORTED, "LDPC graph too large (max_row * m > 65535)");
-        std::vector<uint16_t> row_len(code.m, 0), row_var((size_t)slots, 0), col_ptr(code.n + 1, 0), col_edge, perm(code.n);
+        // pad slots of row_var hold n: est[n] is a byte that is always 0, so the syndrome check runs every row at max_row edges
+        std::vector<uint16_t> row_len(code.m, 0), row_var((size_t)slots, (uint16_t)code.n), col_ptr(code.n + 1, 0), col_edge, perm(code.n);
         for (int r = 0; r < code.m; r++) {
             row_len[r] = (uint16_t)code.mlist[r].size();
             for (size_t j = 0; j < code.mlist[r].size(); j++) row_var[j * code.m + r] = (uint16_t)code.mlist[r][j];

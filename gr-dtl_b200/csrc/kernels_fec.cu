@@ -221,7 +221,7 @@ static __host__ __device__ inline size_t warp_msg_bytes(int n, int slots)
 }
 size_t ldpc_warp_bytes(int n, int slots)
 {
-    return (warp_msg_bytes(n, slots) + (size_t)n * 8 + (size_t)((n + 15) & ~15) + 15) & ~(size_t)15;
+    return (warp_msg_bytes(n, slots) + (size_t)n * 8 + (size_t)((n + 16) & ~15) + 15) & ~(size_t)15;   // est[n] = 0 pad byte
 }
 
 __device__ __forceinline__ WarpBuf carve(unsigned char* base, int n, int slots)
@@ -281,6 +281,23 @@ __device__ __forceinline__ bool syndrome_nonzero_u(const CodeS& c, const uint8_t
         unsigned par = 0;
 #pragma unroll
         for (int j = 0; j < RMAX; j++) if (j < deg) par ^= est[c.row_var()[j * c.m + r]];
+        bad |= (par & 1u) != 0;
+    }
+    return __any_sync(0xffffffffu, bad);
+}
+
+// The same check with every row run at max_row edges, unrolled, no per-lane predicate: the pad slots of row_var point at
+// est[n], a byte the caller keeps at 0.
+template <int RMAX>
+__device__ __forceinline__ bool syndrome_nonzero_pad(const CodeS& c, const uint8_t* est, int lane)
+{
+    const uint16_t* rv = c.row_var();
+    const int m = c.m, mr = c.max_row;
+    bool bad = false;
+    for (int r = lane; r < m; r += 32) {
+        unsigned par = 0;
+#pragma unroll
+        for (int j = 0; j < RMAX; j++) if (j < mr) par ^= est[rv[j * m + r]];
         bad |= (par & 1u) != 0;
     }
     return __any_sync(0xffffffffu, bad);
@@ -409,8 +426,8 @@ __device__ __forceinline__ int bp_loop(const CodeS& c, const WarpBuf& w, int lan
         nit++;
         if (RMAX > 0) bp_iter_unrolled<(RMAX > 0 ? RMAX : 1), (CMAX > 0 ? CMAX : 1)>(c, w, lane);
         else bp_iter_generic(c, w, lane);
-#ifdef DTL_BPV_SYN
-        if (RMAX > 0 ? !syndrome_nonzero_u<(RMAX > 0 ? RMAX : 1)>(c, w.est, lane) : !syndrome_nonzero(c, w.est, lane)) break;
+#ifndef DTL_BPV_NOPAD
+        if (RMAX > 0 ? !syndrome_nonzero_pad<(RMAX > 0 ? RMAX : 1)>(c, w.est, lane) : !syndrome_nonzero(c, w.est, lane)) break;
 #else
         if (!syndrome_nonzero(c, w.est, lane)) break;
 #endif
@@ -422,6 +439,7 @@ __device__ __forceinline__ int bp_loop(const CodeS& c, const WarpBuf& w, int lan
 // filled; returns the iteration count, est[] = final decisions.
 __device__ __forceinline__ int bp_reference_run(const CodeS& c, const WarpBuf& w, int lane, int max_it, double sigma2)
 {
+    if (lane == 0) w.est[c.n] = 0;                                                     // pad byte of the syndrome check
     for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc
         const float m2 = -1 * 2 * w.rx[v];
 #ifndef DTL_BPV_NODIV
