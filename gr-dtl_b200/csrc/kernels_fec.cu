@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(128) tb_plan_kernel(FecParams p)
 // with Q's), lr0[n] double (channel likelihood ratios), est[n] u8.  The received values rx[n] (float) are only
 // needed until lr0 is built and live at the start of the msg area.
 struct CodeS {
-    int n, m, k, rank, slots, max_row, max_col;
+    int n, m, k, rank, slots, edges, max_row, max_col;
     int o_row_len, o_row_var, o_col_ptr, o_col_edge, o_permute;     // byte offsets from the CTA's dynamic shared memory
     const unsigned char* smb;                                       // = the kernel's `sm` (set in the kernel body so the
                                                                     //   compiler keeps the accesses in the shared space)
@@ -252,7 +252,7 @@ __device__ __forceinline__ CodeS stage_code(const CodeDev& g, unsigned char* sm,
     for (int i = threadIdx.x; i < g.edges; i += nthr) col_edge[i] = g.col_edge[i];
     for (int i = threadIdx.x; i < g.n; i += nthr) permute[i] = g.permute[i];
     CodeS c;
-    c.n = g.n; c.m = g.m; c.k = g.k; c.rank = g.rank; c.slots = slots; c.max_row = g.max_row; c.max_col = g.max_col;
+    c.n = g.n; c.m = g.m; c.k = g.k; c.rank = g.rank; c.slots = slots; c.edges = g.edges; c.max_row = g.max_row; c.max_col = g.max_col;
     c.o_row_len = tab_off; c.o_row_var = c.o_row_len + 2 * g.m; c.o_col_ptr = c.o_row_var + 2 * slots;
     c.o_col_edge = c.o_col_ptr + 2 * (g.n + 1); c.o_permute = c.o_col_edge + 2 * g.edges;
     c.smb = sm;
@@ -292,12 +292,12 @@ template <int RMAX>
 __device__ __forceinline__ bool syndrome_nonzero_pad(const CodeS& c, const uint8_t* est, int lane)
 {
     const uint16_t* rv = c.row_var();
-    const int m = c.m, mr = c.max_row;
+    const int m = c.m;
     bool bad = false;
     for (int r = lane; r < m; r += 32) {
         unsigned par = 0;
 #pragma unroll
-        for (int j = 0; j < RMAX; j++) if (j < mr) par ^= est[rv[j * m + r]];
+        for (int j = 0; j < RMAX; j++) par ^= est[rv[j * m + r]];   // RMAX == max_row
         bad |= (par & 1u) != 0;
     }
     return __any_sync(0xffffffffu, bad);
@@ -358,12 +358,14 @@ __device__ __forceinline__ double ddiv_try(double a, double b, bool& ok)
 template <int RMAX, int CMAX>
 __device__ __forceinline__ void bp_iter_unrolled(const CodeS& c, const WarpBuf& w, int lane)
 {
+    // RMAX == max_row.  The pad slots of rows lighter than max_row hold Q = 0.0 (bp_reference_run): t = 2/(1+0) - 1 = 1
+    // exactly and prod * 1 = prod exactly, so every row runs RMAX edges with no per-lane select; only the stores look at deg.
     for (int r = lane; r < c.m; r += 32) {
         const int deg = c.row_len()[r];
         double den[RMAX], t[RMAX];
         bool ok[RMAX], all_ok = true;
 #pragma unroll
-        for (int j = 0; j < RMAX; j++) den[j] = j < deg ? __dadd_rn(1.0, w.msg[j * c.m + r]) : 2.0;
+        for (int j = 0; j < RMAX; j++) den[j] = __dadd_rn(1.0, w.msg[j * c.m + r]);
 #pragma unroll
         for (int j = 0; j < RMAX; j++) { t[j] = ddiv_try(2.0, den[j], ok[j]); all_ok &= ok[j]; }
         if (__builtin_expect(!all_ok, 0)) {
@@ -371,10 +373,10 @@ __device__ __forceinline__ void bp_iter_unrolled(const CodeS& c, const WarpBuf& 
             for (int j = 0; j < RMAX; j++) if (!ok[j]) t[j] = __ddiv_rn(2.0, den[j]);
         }
 #pragma unroll
-        for (int j = 0; j < RMAX; j++) t[j] = j < deg ? __dsub_rn(t[j], 1.0) : 1.0;
+        for (int j = 0; j < RMAX; j++) t[j] = __dsub_rn(t[j], 1.0);
         double prod = 1.0;
 #pragma unroll
-        for (int j = 0; j < RMAX; j++) if (j < deg) prod = __dmul_rn(prod, t[j]);
+        for (int j = 0; j < RMAX; j++) prod = __dmul_rn(prod, t[j]);
         double pp[RMAX];
         all_ok = true;
 #pragma unroll
@@ -471,14 +473,29 @@ __device__ __forceinline__ int bp_reference_run(const CodeS& c, const WarpBuf& w
         }
     }
     __syncwarp();
-    // the unrolled instance that matches the code's degrees exactly (no wasted divisions)
+    if (c.slots != c.edges) {                                                          // pad slots: Q = 0 (see bp_iter_unrolled)
+        for (int e = lane; e < c.slots; e += 32) if (c.row_var()[e] == c.n) w.msg[e] = 0.0;
+        __syncwarp();
+    }
+    // the unrolled instance whose row count IS the code's max_row (pad slots exist for exactly that many edges per row)
     if (c.max_col <= 3) {
-        if (c.max_row <= 4) return bp_loop<4, 3>(c, w, lane, max_it);
-        if (c.max_row <= 6) return bp_loop<6, 3>(c, w, lane, max_it);
-        if (c.max_row <= 8) return bp_loop<8, 3>(c, w, lane, max_it);
+        switch (c.max_row) {
+        case 3: return bp_loop<3, 3>(c, w, lane, max_it);
+        case 4: return bp_loop<4, 3>(c, w, lane, max_it);
+        case 5: return bp_loop<5, 3>(c, w, lane, max_it);
+        case 6: return bp_loop<6, 3>(c, w, lane, max_it);
+        case 7: return bp_loop<7, 3>(c, w, lane, max_it);
+        case 8: return bp_loop<8, 3>(c, w, lane, max_it);
+        default: break;
+        }
     } else if (c.max_col <= 4) {
-        if (c.max_row <= 5) return bp_loop<5, 4>(c, w, lane, max_it);
-        if (c.max_row <= 8) return bp_loop<8, 4>(c, w, lane, max_it);
+        switch (c.max_row) {
+        case 4: return bp_loop<4, 4>(c, w, lane, max_it);
+        case 5: return bp_loop<5, 4>(c, w, lane, max_it);
+        case 6: return bp_loop<6, 4>(c, w, lane, max_it);
+        case 8: return bp_loop<8, 4>(c, w, lane, max_it);
+        default: break;
+        }
     }
     return bp_loop<0, 0>(c, w, lane, max_it);
 }
