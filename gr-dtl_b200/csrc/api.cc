@@ -1042,8 +1042,9 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
         s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
         if (s != DTL_OK) return s;
         if (ov) CK(cudaStreamWaitEvent(h->stream, h->ev_plan, 0));
-        CK(launch_fec(h->stream, fp, h->sm_count, &launches, &h->prof, ov ? 2 : 0));
+        CK(launch_fec(h->stream, fp, h->sm_count, &launches, &h->prof, ov ? 2 : 0, ov ? h->side_stream : nullptr, ov ? h->ev_eq : nullptr));
         h->launches += launches;
+        if (ov) { CK(cudaEventRecord(h->ev_side, h->side_stream)); h->side_pending = true; }
         CK(side_join(h));
         return DTL_OK;
     }

@@ -122,7 +122,10 @@ cudaError_t launch_snr_tags(cudaStream_t st, const EqParams& p);
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
 // phase 0: everything; 1: TB planning only (needs the tags, not the LLRs); 2: what follows the planning
-cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase = 0);
+// side/ev: when given, carry_save_kernel (needs the decoder to be done with the carry buffer, nothing waits for it) runs on
+// `side` behind an event recorded after the BP kernel, beside the TB epilogue; the caller joins `side` afterwards
+cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase = 0,
+                       cudaStream_t side = nullptr, cudaEvent_t ev = nullptr);
 size_t ldpc_warp_bytes(int n, int slots);
 size_t ldpc_tab_bytes(int n, int m, int slots, int edges);
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count);
