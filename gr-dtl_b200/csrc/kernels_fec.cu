@@ -271,21 +271,6 @@ __device__ __forceinline__ bool syndrome_nonzero(const CodeS& c, const uint8_t* 
     return __any_sync(0xffffffffu, bad);
 }
 
-// Same check with the row's edges unrolled and predicated (independent loads, no loop-carried branch).
-template <int RMAX>
-__device__ __forceinline__ bool syndrome_nonzero_u(const CodeS& c, const uint8_t* est, int lane)
-{
-    bool bad = false;
-    for (int r = lane; r < c.m; r += 32) {
-        const int deg = c.row_len()[r];
-        unsigned par = 0;
-#pragma unroll
-        for (int j = 0; j < RMAX; j++) if (j < deg) par ^= est[c.row_var()[j * c.m + r]];
-        bad |= (par & 1u) != 0;
-    }
-    return __any_sync(0xffffffffu, bad);
-}
-
 // The same check with every row run at max_row edges, unrolled, no per-lane predicate: the pad slots of row_var point at
 // est[n], a byte the caller keeps at 0.
 template <int RMAX>
@@ -428,11 +413,7 @@ __device__ __forceinline__ int bp_loop(const CodeS& c, const WarpBuf& w, int lan
         nit++;
         if (RMAX > 0) bp_iter_unrolled<(RMAX > 0 ? RMAX : 1), (CMAX > 0 ? CMAX : 1)>(c, w, lane);
         else bp_iter_generic(c, w, lane);
-#ifndef DTL_BPV_NOPAD
         if (RMAX > 0 ? !syndrome_nonzero_pad<(RMAX > 0 ? RMAX : 1)>(c, w.est, lane) : !syndrome_nonzero(c, w.est, lane)) break;
-#else
-        if (!syndrome_nonzero(c, w.est, lane)) break;
-#endif
     }
     return nit;
 }
@@ -444,21 +425,13 @@ __device__ __forceinline__ int bp_reference_run(const CodeS& c, const WarpBuf& w
     if (lane == 0) w.est[c.n] = 0;                                                     // pad byte of the syndrome check
     for (int v = lane; v < c.n; v += 32) {                                             // rx_lr_calc
         const float m2 = -1 * 2 * w.rx[v];
-#ifndef DTL_BPV_NODIV
         bool ok;
         double q = ddiv_try((double)m2, sigma2, ok);
         if (__builtin_expect(!ok, 0)) q = __ddiv_rn((double)m2, sigma2);
         w.lr0[v] = exp(q);
-#else
-        w.lr0[v] = exp(__ddiv_rn((double)m2, sigma2));
-#endif
     }
     __syncwarp();                                                                      // rx (aliases msg) is dead now
-#ifndef DTL_BPV_NOINIT
     const bool unroll_init = c.max_col <= 4;
-#else
-    const bool unroll_init = false;
-#endif
     if (unroll_init) {                                                                 // spa_initialize, edges unrolled
         for (int v = lane; v < c.n; v += 32) {
             const double lr = w.lr0[v];
