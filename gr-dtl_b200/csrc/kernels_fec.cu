@@ -833,13 +833,6 @@ __global__ void __launch_bounds__(128, 4) ldpc_plain_kernel(LdpcParams p)
 // (slicing-by-4 tables in shared memory) on the words the lanes already hold.
 __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
 {
-    __shared__ uint32_t crc_tab[4][256];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-        uint32_t c = p.crc_table[i];
-        crc_tab[0][i] = c;
-        for (int k = 1; k < 4; k++) { c = p.crc_table[c & 0xffu] ^ (c >> 8); crc_tab[k][i] = c; }
-    }
-    __syncthreads();
     const int lane = threadIdx.x & 31;
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= p.cnt[2]) return;
@@ -852,13 +845,12 @@ __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
 #pragma unroll
     for (int o = 16; o; o >>= 1) nit_sum += __shfl_xor_sync(0xffffffffu, nit_sum, o);
     dtl_tb_result r;
-    r.tb_no = d.tb_no; r.crc_ok = 0; r.nbytes = 0; r.avg_it = nit_sum / d.ncws; r.frame_index = d.frame_index;
+    r.tb_no = d.tb_no; r.crc_ok = 0; r.nbytes = -1; r.avg_it = nit_sum / d.ncws; r.frame_index = d.frame_index;
     if (user >= 0) {
         const uint32_t stored = __ballot_sync(0xffffffffu, bits[user + lane] & 1);   // little-endian CRC field
         __syncwarp();
-        const int words = (user + 31) >> 5, n0 = (user + 7) >> 3;
+        const int words = (user + 31) >> 5;
         const uint32_t* bw = (const uint32_t*)bits;
-        uint32_t crc = 0xFFFFFFFFu;
         for (int w0 = 0; w0 < words; w0 += 32) {
             const int w = w0 + lane;
             uint32_t word = 0;
@@ -873,24 +865,45 @@ __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
             }
             __syncwarp();
             if (w < words) ((uint32_t*)bits)[w] = word;
-            const int nw = min(32, words - w0);
-            for (int i = 0; i < nw; i++) {                                      // all lanes in step: crc is warp-uniform
-                const uint32_t x = __shfl_sync(0xffffffffu, word, i);
-                const int nby = min(4, n0 - 4 * (w0 + i));
-                if (nby == 4) {
-                    const uint32_t y = crc ^ x;
-                    crc = crc_tab[3][y & 0xffu] ^ crc_tab[2][(y >> 8) & 0xffu] ^ crc_tab[1][(y >> 16) & 0xffu] ^ crc_tab[0][y >> 24];
-                } else {
-                    for (int b = 0; b < nby; b++) crc = crc_tab[0][(crc ^ (x >> (8 * b))) & 0xffu] ^ (crc >> 8);
-                }
-            }
             __syncwarp();
         }
-        crc = ~crc;
-        r.crc_ok = crc == stored;
-        r.nbytes = r.crc_ok ? user >> 3 : 0;
+        r.crc_ok = (int)stored; r.nbytes = user;                // tb_crc_kernel turns these into the verdict
     }
     if (lane == 0) p.tres[gi] = r;
+}
+
+// CRC-32 of every released TB: ONE THREAD per TB over the packed words tb_finish_kernel left (slicing-by-4 tables in
+// shared memory).  A warp that runs the byte-serial recurrence together does 32 times the work for the same chain
+// length; here 32 TBs share a warp.
+__global__ void __launch_bounds__(128) tb_crc_kernel(FecParams p)
+{
+    __shared__ uint32_t crc_tab[4][256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        uint32_t c = p.crc_table[i];
+        crc_tab[0][i] = c;
+        for (int k = 1; k < 4; k++) { c = p.crc_table[c & 0xffu] ^ (c >> 8); crc_tab[k][i] = c; }
+    }
+    __syncthreads();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.cnt[2]) return;
+    const int gi = p.tb_list[t];
+    const int user = p.tres[gi].nbytes;
+    if (user < 0) { p.tres[gi].nbytes = 0; return; }
+    const uint32_t stored = (uint32_t)p.tres[gi].crc_ok;
+    const uint32_t* bw = (const uint32_t*)(p.bits + p.tbs[gi].bit_base);
+    const int n0 = (user + 7) >> 3, full = n0 >> 2;
+    uint32_t crc = 0xFFFFFFFFu;
+    for (int i = 0; i < full; i++) {
+        const uint32_t y = crc ^ bw[i];
+        crc = crc_tab[3][y & 0xffu] ^ crc_tab[2][(y >> 8) & 0xffu] ^ crc_tab[1][(y >> 16) & 0xffu] ^ crc_tab[0][y >> 24];
+    }
+    if (n0 & 3) {
+        const uint32_t x = bw[full];
+        for (int b = 0; b < (n0 & 3); b++) crc = crc_tab[0][(crc ^ (x >> (8 * b))) & 0xffu] ^ (crc >> 8);
+    }
+    const int ok = ~crc == stored;
+    p.tres[gi].crc_ok = ok;
+    p.tres[gi].nbytes = ok ? user >> 3 : 0;
 }
 
 // One CTA per stream: concatenate the payload bytes of its CRC-passing TBs in release order
@@ -1005,12 +1018,13 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, side>>>(p);
     }
     const int tb_max = p.n_streams * p.tb_slots;
-    prof->begin(DTL_STAGE_TBFINISH, 3);
+    prof->begin(DTL_STAGE_TBFINISH, 4);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
+    tb_crc_kernel<<<(tb_max + 127) / 128, 128, 0, st>>>(p);
     tb_gather_kernel<<<p.n_streams, 128, 0, st>>>(p);
     if (!(side && ev)) carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     prof->end();
-    if (launches) *launches += 5;
+    if (launches) *launches += 6;
     return cudaGetLastError();
 }
 
