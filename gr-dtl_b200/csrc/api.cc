@@ -86,8 +86,8 @@ struct dtl_b200 {
     // TB planning (needs the tags only) under FFT + equaliser, SNR tags + per-stream feedback state under the LDPC decoder.
     // Off while stage profiling is on (the stage events sit on the main stream) and with DTL_NO_OVERLAP=1.
     cudaStream_t side_stream = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr;
-    bool side_pending = false;
+    cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr, ev_hdr = nullptr;
+    bool side_pending = false, hdr_pending = false;   // hdr_pending: the header branch of this call runs on the side stream
     int overlap = -1;
 
     template <class T> T* upload(const std::vector<T>& v, cudaError_t& e)
@@ -162,7 +162,7 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->out_stream) cudaStreamDestroy(h->out_stream);
     if (h->side_stream) { cudaStreamSynchronize(h->side_stream); cudaStreamDestroy(h->side_stream); }
-    for (cudaEvent_t e : { h->ev_fork, h->ev_plan, h->ev_eq, h->ev_side }) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : { h->ev_fork, h->ev_plan, h->ev_eq, h->ev_side, h->ev_hdr }) if (e) cudaEventDestroy(e);
     if (h->h_err) cudaFreeHost(h->h_err);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -645,7 +645,7 @@ bool side_on(dtl_b200* h)
         h->overlap = (e && atoi(e)) ? 0 : 1;
         if (h->overlap) {
             bool ok = cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) == cudaSuccess;
-            for (cudaEvent_t* ev : { &h->ev_fork, &h->ev_plan, &h->ev_eq, &h->ev_side })
+            for (cudaEvent_t* ev : { &h->ev_fork, &h->ev_plan, &h->ev_eq, &h->ev_side, &h->ev_hdr })
                 ok = ok && cudaEventCreateWithFlags(ev, cudaEventDisableTiming) == cudaSuccess;
             if (!ok) { cudaGetLastError(); h->overlap = 0; }
         }
@@ -750,6 +750,7 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     int eq_launches = 0;
     const bool ov = side_on(h);
     bool tags_due = false;
+    if (h->hdr_pending) { h->hdr_pending = false; CK(cudaStreamWaitEvent(h->stream, h->ev_hdr, 0)); }   // tags + taps come from the side stream
     h->prof.begin(DTL_STAGE_EQ, 1);
     CK(launch_eq(h->stream, p, &eq_launches, ov ? &tags_due : nullptr));
     h->prof.end();
@@ -1238,7 +1239,19 @@ extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_str
     int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
     int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-    if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
+    if (side_on(h)) {
+        // the header branch (instruction-bound) runs on the side stream beside the payload FFT (HBM-bound), which needs neither
+        // tags nor taps; TB planning follows it on the same stream, the equaliser waits for it
+        CK(cudaEventRecord(h->ev_fork, h->stream));
+        CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+        std::swap(h->stream, h->side_stream);
+        s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres);
+        std::swap(h->stream, h->side_stream);
+        if (s != DTL_OK) return s;
+        CK(cudaEventRecord(h->ev_hdr, h->side_stream));
+        CK(cudaEventRecord(h->ev_side, h->side_stream));
+        h->hdr_pending = true; h->side_pending = true;
+    } else if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
     s = rx_device(h, sg, 0, d_iq, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
     if (s != DTL_OK) return s;
     return sg.finish();
