@@ -1152,7 +1152,9 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
     if (mem == DTL_MEM_HOST && F > 0) {
         // chunks of about 48 MB of input, at least 4 of them
         const size_t per_stream = (size_t)F * (in_kind == 0 ? (size_t)h->frame_samples : LN) * sizeof(float2);
-        int Sc = (int)std::max<size_t>(1, ((size_t)48 << 20) / std::max<size_t>(per_stream, 1));
+        static size_t chunk_mb = 0;
+        if (!chunk_mb) { const char* e = getenv("DTL_HOST_CHUNK_MB"); chunk_mb = e && atoi(e) > 0 ? (size_t)atoi(e) : 48; }
+        int Sc = (int)std::max<size_t>(1, (chunk_mb << 20) / std::max<size_t>(per_stream, 1));
         if (S >= 4 * Sc || (S >= 8 && per_stream * S >= ((size_t)16 << 20))) {
             Sc = std::min(Sc, (S + 3) / 4);
             return rx_host_pipelined(h, in_kind, in, taps, meta, S, F, Sc, res, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, frame_crc);
