@@ -125,21 +125,24 @@ __global__ void __launch_bounds__(256) txf_encode_kernel(TxfParams p)
     if (t >= p.ntb[s]) return;
     const TxTb tb = p.tbs[slot];
     if (i >= tb.ncws) return;
-    const CodeDev& c = p.codes[tb.fec_id];
+    const CodeDev& cg = p.codes[tb.fec_id];
+    const int cn = cg.n, ck = cg.k, kwords = cg.kwords;       // into registers: the stores below could alias the table
+    const uint32_t* __restrict__ pmat = cg.pmat;
     uint32_t* dw = encw + wid * p.max_kwords;
     const int len = (tb.payload_bytes + 4) * 8, q = len / tb.ncws, r = len % tb.ncws;
-    const int k_new = q + (i < r), read = i * q + min(i, r), ncheck = c.n - c.k;
-    const uint8_t* d = p.data + (size_t)s * p.in_cap + tb.in_off;
+    const int k_new = q + (i < r), read = i * q + min(i, r), ncheck = cn - ck;
+    const uint8_t* __restrict__ d = p.data + (size_t)s * p.in_cap + tb.in_off;
     const uint32_t crc = p.tbcrc[slot];
-    uint8_t* out = p.tbbits + (size_t)slot * p.maxbits + (size_t)i * ncheck + read;
+    const int pay = tb.payload_bytes;
+    uint8_t* __restrict__ out = p.tbbits + (size_t)slot * p.maxbits + (size_t)i * ncheck + read;
     if ((long long)i * ncheck + read + ncheck + k_new > p.maxbits) return;             // flagged by the planner
-    for (int w = 0; w < c.kwords; w++) {
+    for (int w = 0; w < kwords; w++) {
         const int j = w * 32 + lane;
         unsigned bit = 0;
         if (j < k_new) {
             const int b = read + j;                      // bit of the TB: payload bytes LSB first, then the CRC little-endian
             const int by = b >> 3;
-            const unsigned v = by < tb.payload_bytes ? d[by] : (crc >> (8 * (by - tb.payload_bytes))) & 0xffu;
+            const unsigned v = by < pay ? d[by] : (crc >> (8 * (by - pay))) & 0xffu;
             bit = (v >> (b & 7)) & 1u;
             out[ncheck + j] = (uint8_t)bit;
         }
@@ -148,9 +151,9 @@ __global__ void __launch_bounds__(256) txf_encode_kernel(TxfParams p)
     }
     __syncwarp();
     for (int row = lane; row < ncheck; row += 32) {
-        const uint32_t* pr = c.pmat + (size_t)row * c.kwords;
+        const uint32_t* pr = pmat + (size_t)row * kwords;
         uint32_t acc = 0;
-        for (int w = 0; w < c.kwords; w++) acc ^= __ldg(&pr[w]) & dw[w];
+        for (int w = 0; w < kwords; w++) acc ^= __ldg(&pr[w]) & dw[w];
         out[row] = (uint8_t)(__popc(acc) & 1);
     }
 }
