@@ -540,11 +540,20 @@ __device__ __forceinline__ void gather_cw(const FecParams& p, const TbDesc& d, c
         if (lo < hi) {
             const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
                                           : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
-            for (int g = lo + lane; g < hi; g += 32) {
-                const float x = -1 * __ldcs(&src[g - base]);
-                const int col = c.permute()[g - rcv_idx];
-                rx[col] = x;
-                est[col] = x < 0.f ? 1 : 0;
+            for (int g0 = lo + lane; g0 < hi; g0 += 128) {           // four loads in flight per lane
+                float xv[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) { const int g = g0 + 32 * u; xv[u] = g < hi ? __ldcs(&src[g - base]) : 0.f; }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int g = g0 + 32 * u;
+                    if (g < hi) {
+                        const float x = -1 * xv[u];
+                        const int col = c.permute()[g - rcv_idx];
+                        rx[col] = x;
+                        est[col] = x < 0.f ? 1 : 0;
+                    }
+                }
             }
         }
         base += sg.len;
