@@ -87,7 +87,8 @@ struct dtl_b200 {
     // Off while stage profiling is on (the stage events sit on the main stream) and with DTL_NO_OVERLAP=1.
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr, ev_hdr = nullptr;
-    bool side_pending = false, hdr_pending = false;   // hdr_pending: the header branch of this call runs on the side stream
+    bool side_pending = false, hdr_pending = false;
+    const float2* fuse_iq = nullptr;  // set by rx_device for one dev_equalize call: FFT fused into the equaliser kernel   // hdr_pending: the header branch of this call runs on the side stream
     int overlap = -1;
 
     template <class T> T* upload(const std::vector<T>& v, cudaError_t& e)
@@ -148,7 +149,7 @@ extern "C" const char* dtl_b200_last_error(const dtl_b200* h)
 extern "C" void dtl_b200_destroy(dtl_b200* h)
 {
     if (!h) return;
-    cudaSetDevice(h->device);
+    if (cudaSetDevice(h->device) != cudaSuccess) { cudaGetLastError(); delete h; return; }   // runtime unloading: nothing to free
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
@@ -745,6 +746,10 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr;
     p.bytes = fbytes; p.bytes_stride = h->bytes_stride; p.nbytes = fnbytes; p.crc_ok = fcrc;
     p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
+    if (h->fuse_iq) {
+        p.iq = h->fuse_iq; p.iq_frame_stride = h->frame_samples; p.iq_sym0 = h->H + 2; p.iq_sym_stride = h->N + h->cp; p.iq_skip = h->cp;
+        h->fuse_iq = nullptr;
+    }
     p.mag = sg.scratch<float>(SL_MAG, (size_t)n * (size_t)std::max(h->pl.npil_frame, 1));     // |pilot_eq| for snr_tags_kernel
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "scratch");
     int eq_launches = 0;
@@ -1033,13 +1038,21 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
             CK(cudaEventRecord(h->ev_plan, h->side_stream));
         }
     }
-    if (in_kind == 0) {
+    bool fused = false;
+    if (in_kind == 0 && h->fec_enabled && !h->prof.on) {     // stage profiling keeps FFT and equaliser apart
+        EqParams probe;
+        memset(&probe, 0, sizeof probe);
+        probe.pl = h->pl; probe.iq = d_in; probe.llr = d_llr;
+        fused = eq_can_fuse_fft(probe);
+    }
+    if (in_kind == 0 && !fused) {
         float2* fq = sg.scratch<float2>(SL_FREQ, n * LN);
         if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
         if ((s = dev_demod(h, d_in, (long long)n, fq)) != DTL_OK) return s;
         d_freq = fq;
     }
     if (h->fec_enabled) {
+        if (fused) { h->fuse_iq = d_in; d_freq = nullptr; }
         s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
         if (s != DTL_OK) return s;
         if (ov) CK(cudaStreamWaitEvent(h->stream, h->ev_plan, 0));

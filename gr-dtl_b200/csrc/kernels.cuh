@@ -35,7 +35,11 @@ struct EqParams {
     const float2* tw;
     int use_tma;                                   // set by the launcher: source 16-byte aligned
     float* mag;                                    // [n_frames][npil_frame] scratch: |pilot_eq| (eq_fast_kernel -> snr_tags_kernel)
+    // fused CP strip + FFT (eq_fast_kernel, fft_len 64): time-domain frames instead of `freq`
+    const float2* iq; long long iq_frame_stride; int iq_sym0, iq_sym_stride, iq_skip;
 };
+// true when launch_eq would run the lean kernel with the FFT fused in for these parameters (p.iq set, p.freq unused)
+bool eq_can_fuse_fft(const EqParams& p);
 
 // ---- per-stream sequential bookkeeping ------------------------------------------------------------------
 struct StreamParams {
@@ -136,3 +140,31 @@ cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int byte
                                 uint8_t* out, int cap, int* out_n, int* err);
 
 } // namespace dtl
+
+#ifdef __CUDACC__
+// 8-point forward DFT in registers (radix-2 then two radix-4), used by the 64-point FFT (8 x 8) in kernels_fft.cu and by
+// the equaliser kernel when the FFT is fused into it.
+__device__ __forceinline__ void dft8_fwd(float2 (&x)[8])
+{
+    const float r = 0.70710678118654752440f;
+#define DTL_ADD(a, b) make_float2((a).x + (b).x, (a).y + (b).y)
+#define DTL_SUB(a, b) make_float2((a).x - (b).x, (a).y - (b).y)
+    const float2 a0 = DTL_ADD(x[0], x[4]), a1 = DTL_ADD(x[1], x[5]), a2 = DTL_ADD(x[2], x[6]), a3 = DTL_ADD(x[3], x[7]);
+    const float2 b0 = DTL_SUB(x[0], x[4]), t1 = DTL_SUB(x[1], x[5]), t2 = DTL_SUB(x[2], x[6]), t3 = DTL_SUB(x[3], x[7]);
+    const float2 b1 = make_float2((t1.x + t1.y) * r, (t1.y - t1.x) * r);        // * W8^1 = (1 - i)/sqrt 2
+    const float2 b2 = make_float2(t2.y, -t2.x);                                 // * W8^2 = -i
+    const float2 b3 = make_float2((t3.y - t3.x) * r, -(t3.x + t3.y) * r);       // * W8^3 = (-1 - i)/sqrt 2
+    {   // 4-point DFT of a -> X0, X2, X4, X6
+        const float2 s0 = DTL_ADD(a0, a2), d0 = DTL_SUB(a0, a2), s1 = DTL_ADD(a1, a3), u = DTL_SUB(a1, a3);
+        const float2 d1 = make_float2(u.y, -u.x);
+        x[0] = DTL_ADD(s0, s1); x[2] = DTL_ADD(d0, d1); x[4] = DTL_SUB(s0, s1); x[6] = DTL_SUB(d0, d1);
+    }
+    {   // 4-point DFT of b -> X1, X3, X5, X7
+        const float2 s0 = DTL_ADD(b0, b2), d0 = DTL_SUB(b0, b2), s1 = DTL_ADD(b1, b3), u = DTL_SUB(b1, b3);
+        const float2 d1 = make_float2(u.y, -u.x);
+        x[1] = DTL_ADD(s0, s1); x[3] = DTL_ADD(d0, d1); x[5] = DTL_SUB(s0, s1); x[7] = DTL_SUB(d0, d1);
+    }
+#undef DTL_ADD
+#undef DTL_SUB
+}
+#endif

@@ -100,30 +100,6 @@ __global__ void __launch_bounds__(256) fft_fwd_kernel(const float2* __restrict__
 // its warp); lane ka then does the outer 8-point DFT and stores X[ka + 8 kb] -- 64 contiguous bytes per symbol and
 // instruction on both sides.  No CTA barrier, no staging of input or output, twiddles live in registers across the
 // grid-stride loop.
-__device__ __forceinline__ void dft8_fwd(float2 (&x)[8])
-{
-    const float r = 0.70710678118654752440f;
-#define DTL_ADD(a, b) make_float2((a).x + (b).x, (a).y + (b).y)
-#define DTL_SUB(a, b) make_float2((a).x - (b).x, (a).y - (b).y)
-    const float2 a0 = DTL_ADD(x[0], x[4]), a1 = DTL_ADD(x[1], x[5]), a2 = DTL_ADD(x[2], x[6]), a3 = DTL_ADD(x[3], x[7]);
-    const float2 b0 = DTL_SUB(x[0], x[4]), t1 = DTL_SUB(x[1], x[5]), t2 = DTL_SUB(x[2], x[6]), t3 = DTL_SUB(x[3], x[7]);
-    const float2 b1 = make_float2((t1.x + t1.y) * r, (t1.y - t1.x) * r);        // * W8^1 = (1 - i)/sqrt 2
-    const float2 b2 = make_float2(t2.y, -t2.x);                                 // * W8^2 = -i
-    const float2 b3 = make_float2((t3.y - t3.x) * r, -(t3.x + t3.y) * r);       // * W8^3 = (-1 - i)/sqrt 2
-    {   // 4-point DFT of a -> X0, X2, X4, X6
-        const float2 s0 = DTL_ADD(a0, a2), d0 = DTL_SUB(a0, a2), s1 = DTL_ADD(a1, a3), u = DTL_SUB(a1, a3);
-        const float2 d1 = make_float2(u.y, -u.x);
-        x[0] = DTL_ADD(s0, s1); x[2] = DTL_ADD(d0, d1); x[4] = DTL_SUB(s0, s1); x[6] = DTL_SUB(d0, d1);
-    }
-    {   // 4-point DFT of b -> X1, X3, X5, X7
-        const float2 s0 = DTL_ADD(b0, b2), d0 = DTL_SUB(b0, b2), s1 = DTL_ADD(b1, b3), u = DTL_SUB(b1, b3);
-        const float2 d1 = make_float2(u.y, -u.x);
-        x[1] = DTL_ADD(s0, s1); x[3] = DTL_ADD(d0, d1); x[5] = DTL_SUB(s0, s1); x[7] = DTL_SUB(d0, d1);
-    }
-#undef DTL_ADD
-#undef DTL_SUB
-}
-
 __global__ void __launch_bounds__(256) fft64_fwd_kernel(const float2* __restrict__ in, float2* __restrict__ out,
                                                           unsigned n_sym, unsigned syms_per_frame, long long in_frame_stride,
                                                           int in_sym0, int in_sym_stride, int in_skip,

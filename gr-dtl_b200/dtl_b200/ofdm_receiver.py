@@ -140,6 +140,9 @@ class ofdm_receiver:
 
     def __del__(self):
         try:
+            import sys
+            if sys is None or sys.is_finalizing():      # interpreter teardown: the CUDA runtime may already be gone
+                return
             self.close()
         except Exception:
             pass
