@@ -7,6 +7,7 @@
 //               8PSK[0], BPSK[0] which the metric golden 6.568538665771484 pins).
 //   Extension:  QAM64 / QAM256 (enum 5/6) do not exist in the reference; Gray-coded
 //               square QAM, unit average energy, index = (gray(im level) << b/2) | gray(re level).
+#include <vector>
 #include "oracle.hpp"
 #include <cmath>
 #include <stdexcept>
@@ -69,9 +70,13 @@ static constellation make(int type)
 
 const constellation& get_constellation(int cnst)
 {
-    static constellation all[MAX_CNST + 1];
-    static bool init = false;
-    if (!init) { for (int i = 1; i <= MAX_CNST; i++) all[i] = make(i); init = true; }
+    // built once under the compiler's thread-safe static initialisation: the batch entry points call this from several
+    // worker threads at once, and a hand-rolled "init" flag here let a second thread rebuild the tables under a reader
+    static const std::vector<constellation> all = [] {
+        std::vector<constellation> v(MAX_CNST + 1);
+        for (int i = 1; i <= MAX_CNST; i++) v[i] = make(i);
+        return v;
+    }();
     if (cnst < 1 || cnst > MAX_CNST) throw std::invalid_argument("Invalid constellation");
     return all[cnst];
 }
