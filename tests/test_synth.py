@@ -59,3 +59,35 @@ def test_synth_round_trip_gpu_and_oracle(cnst, snr, fec):
         assert np.array_equal(gb, want), "stream %d" % s
     assert np.array_equal(got["res"]["fb_cnst"], ref["res"]["fb_cnst"])
     rx.close()
+
+
+@pytest.mark.parametrize("cnst", [1, 2, 3, 4, 5, 6])
+def test_oracle_framer_with_caller_bytes_matches_fec_plan_and_is_continuous(cnst):
+    """The oracle framer fed with the caller's bytes (the reference for dtl_b200_fec_frame, tests/test_gpu_fec_frame.py):
+    its tags equal the product's framing plan, it consumes exactly the TB payloads it started, and F frames in one call
+    equal the same frames in two calls (the TB in flight continues)."""
+    from dtl_b200 import synth
+    ocfg = make_oracle_cfg(alists=(ALIST_300,), initial_mcs=0, cnsts=(1, 2, 3, 4, 5, 6))
+    S, F = 3, 12
+    rng = np.random.default_rng(100 + cnst)
+    data = rng.integers(0, 256, size=(S, F * 1200), dtype=np.uint8)
+    c = np.full(S * F, cnst, dtype=np.int32)
+    f = np.ones(S * F, dtype=np.int32)
+    one = ocfg.frame_batch(data, c, f, S, F)
+    p = synth.fec_plan(F, ocfg.capacity, orc.bps(cnst), 300, 152, 1)
+    m = p.meta.copy()
+    m["constellation"] = cnst
+    for s in range(S):
+        for name in m.dtype.names:
+            assert np.array_equal(one["meta"][name].reshape(S, F)[s], m[name]), name
+    assert np.all(one["started"] == len(p.tb_bits))
+    assert np.all(one["consumed"] == sum(p.tb_payload_bytes))
+    state, pos, parts = None, np.zeros(S, dtype=np.int64), []
+    for h in range(2):
+        d = np.stack([data[s, pos[s]:pos[s] + 8000] for s in range(S)])
+        r = ocfg.frame_batch(d, c.reshape(S, F)[:, h * 6:(h + 1) * 6].reshape(-1), np.ones(S * 6, dtype=np.int32), S, 6, state=state)
+        state = r["state"]
+        pos += r["consumed"]
+        parts.append(r["chunks"].reshape(S, 6, -1))
+    assert np.array_equal(np.concatenate(parts, axis=1).reshape(S * F, -1), one["chunks"])
+    assert np.array_equal(pos, one["consumed"])
