@@ -24,6 +24,7 @@
 // sum-product on likelihood ratios, IEEE double, products in alist order) so payload bits AND iteration
 // counts match the reference; DTL_LDPC_LAYERED is a layered normalised min-sum in fp32 (throughput mode).
 #include "kernels.cuh"
+#include <cstdlib>
 
 namespace dtl {
 
@@ -1004,7 +1005,9 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
             attr_set = smem;
         }
         prof->begin(DTL_STAGE_LDPC, 2);
-        ldpc_screen_kernel<<<sm_count * 8, 256, smem, st>>>(p);
+        static int per_sm_screen = 0;                // CTAs per SM of the grid-stride screening pass (6 are resident at 40 registers)
+        if (!per_sm_screen) { const char* e = getenv("DTL_SCREEN_CTAS"); per_sm_screen = e && atoi(e) > 0 ? atoi(e) : 8; }
+        ldpc_screen_kernel<<<sm_count * per_sm_screen, 256, smem, st>>>(p);
     }
     {   // pass 2: belief propagation on what did not pass, persistent
         const int warps = DTL_BP_WARPS;
