@@ -877,32 +877,24 @@ __global__ void __launch_bounds__(256) tb_finish_kernel(FecParams p)
             if (w < words) ((uint32_t*)bits)[w] = word;
             __syncwarp();
         }
-        r.crc_ok = (int)stored; r.nbytes = user;                // tb_crc_kernel turns these into the verdict
+        r.crc_ok = (int)stored; r.nbytes = user;                // tb_gather_kernel (tb_crc_one) turns these into the verdict
     }
     if (lane == 0) p.tres[gi] = r;
 }
 
-// CRC-32 of every released TB: ONE THREAD per TB over the packed words tb_finish_kernel left (slicing-by-4 tables in
-// shared memory).  A warp that runs the byte-serial recurrence together does 32 times the work for the same chain
-// length; here 32 TBs share a warp.
-__global__ void __launch_bounds__(128) tb_crc_kernel(FecParams p)
+// CRC-32 of a released TB by ONE THREAD over the packed words tb_finish_kernel left (slicing-by-4 tables in shared
+// memory).  A warp that runs the byte-serial recurrence together does 32 times the work for the same chain length; in
+// tb_gather_kernel the TBs of a stream share the CTA instead.  r.nbytes holds the TB's user bits (-1: none), r.crc_ok the
+// stored CRC on entry; both become the verdict.
+__device__ __forceinline__ void tb_crc_one(const FecParams& p, int gi, dtl_tb_result& r, const uint32_t (*crc_tab)[256])
 {
-    __shared__ uint32_t crc_tab[4][256];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-        uint32_t c = p.crc_table[i];
-        crc_tab[0][i] = c;
-        for (int k = 1; k < 4; k++) { c = p.crc_table[c & 0xffu] ^ (c >> 8); crc_tab[k][i] = c; }
-    }
-    __syncthreads();
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= p.cnt[2]) return;
-    const int gi = p.tb_list[t];
-    const int user = p.tres[gi].nbytes;
-    if (user < 0) { p.tres[gi].nbytes = 0; return; }
-    const uint32_t stored = (uint32_t)p.tres[gi].crc_ok;
+    const int user = r.nbytes;
+    if (user < 0) { r.crc_ok = 0; r.nbytes = 0; return; }
+    const uint32_t stored = (uint32_t)r.crc_ok;
     const uint32_t* bw = (const uint32_t*)(p.bits + p.tbs[gi].bit_base);
     const int n0 = (user + 7) >> 3, full = n0 >> 2;
     uint32_t crc = 0xFFFFFFFFu;
+#pragma unroll 4
     for (int i = 0; i < full; i++) {
         const uint32_t y = crc ^ bw[i];
         crc = crc_tab[3][y & 0xffu] ^ crc_tab[2][(y >> 8) & 0xffu] ^ crc_tab[1][(y >> 16) & 0xffu] ^ crc_tab[0][y >> 24];
@@ -912,8 +904,8 @@ __global__ void __launch_bounds__(128) tb_crc_kernel(FecParams p)
         for (int b = 0; b < (n0 & 3); b++) crc = crc_tab[0][(crc ^ (x >> (8 * b))) & 0xffu] ^ (crc >> 8);
     }
     const int ok = ~crc == stored;
-    p.tres[gi].crc_ok = ok;
-    p.tres[gi].nbytes = ok ? user >> 3 : 0;
+    r.crc_ok = ok;
+    r.nbytes = ok ? user >> 3 : 0;
 }
 
 // One CTA per stream: concatenate the payload bytes of its CRC-passing TBs in release order
@@ -927,9 +919,18 @@ __global__ void __launch_bounds__(128) tb_gather_kernel(FecParams p)
     const int s = blockIdx.x;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, warps = blockDim.x >> 5;
     const int ntb = min(p.tb_count[s], DTL_GATHER_MAXTB);
+    __shared__ uint32_t crc_tab[4][256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        uint32_t c = p.crc_table[i];
+        crc_tab[0][i] = c;
+        for (int k = 1; k < 4; k++) { c = p.crc_table[c & 0xffu] ^ (c >> 8); crc_tab[k][i] = c; }
+    }
+    __syncthreads();
     for (int i = threadIdx.x; i < ntb; i += blockDim.x) {
         const int gi = s * p.tb_slots + i;
-        const dtl_tb_result r = p.tres[gi];
+        dtl_tb_result r = p.tres[gi];
+        tb_crc_one(p, gi, r, crc_tab);
+        p.tres[gi] = r;
         if (p.tb_out && i < p.tb_cap) p.tb_out[(size_t)s * p.tb_cap + i] = r;
         s_nb[i] = r.nbytes; s_bb[i] = p.tbs[gi].bit_base;
     }
@@ -1030,13 +1031,12 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, side>>>(p);
     }
     const int tb_max = p.n_streams * p.tb_slots;
-    prof->begin(DTL_STAGE_TBFINISH, 4);
+    prof->begin(DTL_STAGE_TBFINISH, 3);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
-    tb_crc_kernel<<<(tb_max + 127) / 128, 128, 0, st>>>(p);
     tb_gather_kernel<<<p.n_streams, 128, 0, st>>>(p);
     if (!(side && ev)) carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
     prof->end();
-    if (launches) *launches += 6;
+    if (launches) *launches += 5;
     return cudaGetLastError();
 }
 
