@@ -521,6 +521,9 @@ extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
     if ((e = cudaGetDeviceProperties(&prop, h->device)) != cudaSuccess) { cuda_fail(h, e, "cudaGetDeviceProperties"); return bail(DTL_ERR_CUDA); }
     if (prop.major != 10) { fail(h, DTL_ERR_UNSUPPORTED, "libdtl_b200 is built for sm_100a only"); return bail(DTL_ERR_UNSUPPORTED); }
     h->sm_count = prop.multiProcessorCount;
+    // per-device kernel attributes (opt-in dynamic shared memory), set for THIS handle's device
+    for (cudaError_t (*init)() : { init_kernels_fft, init_kernels_eq, init_kernels_fec, init_kernels_hdr })
+        if ((e = init()) != cudaSuccess) { cuda_fail(h, e, "cudaFuncSetAttribute"); return bail(DTL_ERR_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { cuda_fail(h, e, "cudaStreamCreate"); return bail(DTL_ERR_CUDA); }
     h->prof.st = h->stream;
     h->N = N; h->cp = c->cp_len; h->L = c->frame_len; h->H = c->header_syms > 0 ? c->header_syms : (c->fec_enabled ? 2 : 1);
@@ -1075,6 +1078,9 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
         h->launches += 1;
     }
     if (d_nt) CK(cudaMemsetAsync(d_nt, 0, (size_t)S * sizeof(int), h->stream));
+    // the SNR tags and the per-stream feedback state were put on the side stream by dev_equalize: everything that reads
+    // `res` after this call (the D2H copies of rx_host_pipelined included) is ordered behind the main stream
+    CK(side_join(h));
     return DTL_OK;
 }
 

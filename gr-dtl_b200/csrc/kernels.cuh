@@ -4,6 +4,15 @@
 
 namespace dtl {
 
+#define DTL_MAX_DYN_SMEM (227 * 1024)   // opt-in dynamic shared memory per CTA on sm_100
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: each init_kernels_* sets it for the kernels of its
+// translation unit on the CURRENT device; dtl_b200_create calls them after cudaSetDevice, so handles on several GPUs of
+// one process all find it set.
+cudaError_t init_kernels_eq();
+cudaError_t init_kernels_fec();
+cudaError_t init_kernels_hdr();
+cudaError_t init_kernels_fft();
+
 #define DTL_MAX_SMEM_CODES 5     // codes 1..4 get their graph tables staged in shared memory
 
 __host__ __device__ inline int log2n_of(int n) { int l = 0; while ((1 << l) < n) l++; return l; }

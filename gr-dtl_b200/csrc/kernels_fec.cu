@@ -1000,11 +1000,6 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     }
     {   // pass 1: screening, grid-stride over the codeword work list
         const size_t smem = (size_t)p.screen_tab_bytes + 8 * (size_t)p.screen_bytes;
-        static size_t attr_set = 0;
-        if (smem > 48 * 1024 && smem > attr_set) {
-            cudaFuncSetAttribute(ldpc_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            attr_set = smem;
-        }
         prof->begin(DTL_STAGE_LDPC, 2);
         static int per_sm_screen = 0;                // CTAs per SM of the grid-stride screening pass (6 are resident at 40 registers)
         if (!per_sm_screen) { const char* e = getenv("DTL_SCREEN_CTAS"); per_sm_screen = e && atoi(e) > 0 ? atoi(e) : 8; }
@@ -1014,11 +1009,6 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         const int warps = DTL_BP_WARPS;
         const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
         if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-        static size_t attr_set = 0;
-        if (smem > 48 * 1024 && smem > attr_set) {
-            cudaFuncSetAttribute(ldpc_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            attr_set = smem;
-        }
         int per_sm = (int)((226 * 1024) / (smem + 1024));
         if (per_sm < 1) per_sm = 1;
         if (per_sm > 8) per_sm = 8;
@@ -1042,17 +1032,22 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
 
 __global__ void cursor_clear_kernel(int* c) { *c = 0; }
 
+// Function attributes are per device: dtl_b200_create calls this after cudaSetDevice for every handle.
+cudaError_t init_kernels_fec()
+{
+    const int mx = DTL_MAX_DYN_SMEM;
+    cudaError_t e = cudaFuncSetAttribute(ldpc_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ldpc_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(ldpc_plain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    return e;
+}
+
 cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
 {
     if (p.count <= 0) return cudaSuccess;
     const int warps = 4;
     const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
     if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-    static size_t attr_set = 0;
-    if (smem > 48 * 1024 && smem > attr_set) {
-        cudaFuncSetAttribute(ldpc_plain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = smem;
-    }
     int per_sm = (int)((226 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 8) per_sm = 8;

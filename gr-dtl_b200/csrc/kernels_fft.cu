@@ -241,7 +241,6 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
     const int T = N / 4, threads = T >= 256 ? T : 256, G = threads / T;
     const long long blocks = (n_sym + G - 1) / G;
     const size_t smem = (size_t)G * 2 * N * sizeof(float2);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(fft_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fft_fwd_kernel<<<(unsigned)blocks, threads, smem, st>>>(in, out, n_sym, syms_per_frame, in_frame_stride, in_sym0,
                                                           in_sym_stride, in_skip, N, ilog2(N), tw);
     return cudaGetLastError();
@@ -253,7 +252,6 @@ cudaError_t launch_fft_inv(cudaStream_t st, const float2* in, float2* out, long 
     const int T = N / 4, threads = T >= 256 ? T : 256, G = threads / T;
     const long long blocks = (n_sym + G - 1) / G;
     const size_t smem = (size_t)G * 2 * N * sizeof(float2);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(fft_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     fft_inv_kernel<<<(unsigned)blocks, threads, smem, st>>>(in, out, n_sym, N, ilog2(N), tw);
     return cudaGetLastError();
 }
@@ -265,9 +263,16 @@ cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p)
     const long long n_sym = p.n_frames * (2 + p.H + p.L);
     const long long blocks = (n_sym + G - 1) / G;
     const size_t smem = (size_t)G * 2 * N * sizeof(float2);
-    if (smem > 48 * 1024) cudaFuncSetAttribute(tx_mod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     tx_mod_kernel<<<(unsigned)blocks, threads, smem, st>>>(p);
     return cudaGetLastError();
+}
+
+cudaError_t init_kernels_fft()
+{
+    cudaError_t e = cudaFuncSetAttribute(fft_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(fft_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tx_mod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
+    return e;
 }
 
 } // namespace dtl

@@ -231,11 +231,14 @@ cudaError_t launch_header(cudaStream_t st, const HdrParams& p)
     const size_t smem = group * G;
     const long long ctas = (p.n_frames + G - 1) / G;
     if (smem > 200 * 1024 || ctas > 0x7fffffffLL) return cudaErrorInvalidConfiguration;
-    static size_t attr = 0;
-    if (smem > 48 * 1024 && smem > attr) { cudaFuncSetAttribute(header_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = smem; }
     header_kernel<<<(unsigned)ctas, tpf * G, smem, st>>>(p, G, (int)group);
     header_fix_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
     return cudaGetLastError();
+}
+
+cudaError_t init_kernels_hdr()
+{
+    return cudaFuncSetAttribute(header_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
 }
 
 } // namespace dtl

@@ -33,6 +33,20 @@ def build(force=False):
     return _LIB_PATH
 
 
+def build_native():
+    """-O3 -march=native build on THIS machine (bench.py's CPU arm: the timed baseline is compiled for the host it runs
+    on); falls back to the portable library when the compiler is missing.  Call before lib()."""
+    global _LIB_PATH
+    native = os.path.join(_HERE, "_build", "liboracle_native.so")
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "native"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        if _lib is None:
+            _LIB_PATH = native
+        return "-O3 -march=native (built on this host)"
+    except Exception:
+        return "-O3 -march=x86-64-v3 (portable build; native build failed on this host)"
+
+
 _lib = None
 
 

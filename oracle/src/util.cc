@@ -118,7 +118,10 @@ void feedback_decision::get_feedback(double snr, int* c, int* f)
 {
     int id = last;
     if (snr < snr_th[id]) {
-        update_decision(id - 1);
+        // :70 `assert(current_mcs_id > 0)`: undefined in a release build when the estimate is <= 0 dB at MCS 0; this
+        // restatement (and the CUDA path) define it as "no change, counter cleared"
+        if (id > 0) update_decision(id - 1);
+        else counter = 0;
     } else if ((size_t)(id + 1) < snr_th.size()) {
         if (snr > snr_th[id + 1] + hysteresis) update_decision(id + 1);
         else counter = 0;
