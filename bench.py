@@ -157,7 +157,7 @@ def run_reference(a):
 # ---- the GPU arm ------------------------------------------------------------------------------------------------
 def product_config(a):
     import dtl_b200
-    th = {1: sys.float_info.min, 2: 13, 3: 18, 4: 23, 5: 28, 6: 33}           # examples/config_fec.json thresholds
+    th = {1: sys.float_info.min, 2: 13, 3: 18, 4: 23, 5: 28, 6: 33}           # examples/config.json:3-6 thresholds (+5 dB per extension row)
     cn = tuple(sorted({1, 2, 3, 4, a.cnst}))
     mcs = [(th[c], (dtl_b200.constellation_type_t(c), "fec_1")) for c in cn]
     mcs[0] = (sys.float_info.min, mcs[0][1])

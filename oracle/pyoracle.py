@@ -269,6 +269,12 @@ class Config:
             lib().orc_cfg_destroy(self.h)
             self.h = None
 
+    def set_literal(self, on=True):
+        """rx_batch's payload equaliser evaluates the reference's own std::complex<float> expressions
+        (lib/dtl/ofdm_adaptive_equalizer.cc:241-256) instead of the arithmetic contract of src/contract.hpp"""
+        lib().orc_cfg_set_literal(self.h, int(on))
+        return self
+
     # ---- LDPC ----
     def code_info(self, fec_id):
         N, K, M = C.c_int(0), C.c_int(0), C.c_int(0)

@@ -136,6 +136,7 @@ int orc_cfg_add_code(void* h, const char* alist_path)
     return (int)b->c.codes.size() - 1;
 }
 void orc_cfg_set_fec(void* h, int fec) { ((cfg_box*)h)->c.fec = fec != 0; }
+void orc_cfg_set_literal(void* h, int lit) { ((cfg_box*)h)->c.eq_literal = lit != 0; }
 void orc_cfg_set_mcs(void* h, int n, const double* snr, const int* cnst, const int* fec, int initial)
 {
     stream_cfg& c = ((cfg_box*)h)->c;

@@ -250,6 +250,7 @@ rx_stream::rx_stream(const stream_cfg& c)
     : cfg(c), feq(make_payload_cfg(c), feedback_decision(1.0, 5, c.mcs_snr, c.mcs_cnst, c.mcs_fec, c.initial_mcs)),
       crc(4, 0x04C11DB7, 0xFFFFFFFF, 0xFFFFFFFF)
 {
+    feq.eq.literal = cfg.eq_literal;
     if (cfg.fec) {
         int max_bps = 0;
         for (int x : cfg.constellations) max_bps = std::max(max_bps, bits_per_symbol(x));

@@ -21,6 +21,7 @@ struct stream_cfg {
     ofdm_cfg ofdm;
     int frame_len = 20;
     bool fec = false;
+    bool eq_literal = false;                       // payload equaliser runs the reference's literal std::complex expressions
     std::vector<const ldpc_code*> codes;           // [0] = nullptr (ldpc_dec.cc:25)
     std::vector<int> constellations;               // allowed set
     std::vector<double> mcs_snr; std::vector<int> mcs_cnst, mcs_fec; int initial_mcs = 0;

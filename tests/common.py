@@ -14,21 +14,23 @@ ALIST_100_27 = os.path.join(GOLDEN, "n_0100_k_0027_gap_04.alist")
 DBL_MIN = sys.float_info.min
 
 
-def mcs_table(cnsts, fec):
-    """(snr threshold, (constellation, fec id)) rows: thresholds of examples/config.json / config_fec.json"""
-    th = {1: DBL_MIN, 2: 13, 3: 18, 4: 23, 5: 28, 6: 33}
+def mcs_table(cnsts, fec, lut="config"):
+    """(snr threshold, (constellation, fec id)) rows.  lut "config": the thresholds of examples/config.json:3-6 (13 / 18 / 23 dB;
+    every test that does not say otherwise, FEC or not); lut "config_fec": examples/config_fec.json:4-7 (11 / 16 / 21 dB, what
+    BASELINE.json configs[1] ships with).  The 64-/256-QAM rows (+5 dB each) are this repo's extension."""
+    th = {1: DBL_MIN, 2: 13, 3: 18, 4: 23, 5: 28, 6: 33} if lut == "config" else {1: DBL_MIN, 2: 11, 3: 16, 4: 21, 5: 26, 6: 31}
     rows = [(th[c], (c, 1 if fec else 0)) for c in sorted(cnsts)]
     rows[0] = (DBL_MIN, rows[0][1])
     return rows
 
 
-def make_oracle_cfg(fft_len=64, frame_len=20, alists=(), cnsts=(1, 2, 3, 4), initial_mcs=0, cp_len=None):
+def make_oracle_cfg(fft_len=64, frame_len=20, alists=(), cnsts=(1, 2, 3, 4), initial_mcs=0, cp_len=None, lut="config"):
     import pyoracle as orc
     return orc.Config(fft_len=fft_len, cp_len=cp_len, frame_len=frame_len, alists=list(alists),
-                      mcs=mcs_table(cnsts, bool(alists)), initial_mcs=initial_mcs, constellations=tuple(cnsts))
+                      mcs=mcs_table(cnsts, bool(alists), lut), initial_mcs=initial_mcs, constellations=tuple(cnsts))
 
 
-def make_product_cfg(fft_len=64, frame_len=20, alists=(), cnsts=(1, 2, 3, 4), initial_mcs=0, cp_len=None):
+def make_product_cfg(fft_len=64, frame_len=20, alists=(), cnsts=(1, 2, 3, 4), initial_mcs=0, cp_len=None, lut="config"):
     import dtl_b200
     kw = {}
     if fft_len != 64:
@@ -36,7 +38,7 @@ def make_product_cfg(fft_len=64, frame_len=20, alists=(), cnsts=(1, 2, 3, 4), in
         kw = dict(occupied_carriers=occ, pilot_carriers=pil)
     names = ["fec_%d" % (i + 1) for i in range(len(alists))]
     mcs = tuple((snr, (dtl_b200.constellation_type_t(c), names[f - 1] if f else "no_fec"))
-                for snr, (c, f) in mcs_table(cnsts, bool(alists)))
+                for snr, (c, f) in mcs_table(cnsts, bool(alists), lut))
     return dtl_b200.ofdm_adaptive_rx_config(fft_len=fft_len, cp_len=cp_len if cp_len is not None else fft_len // 4,
                                             frame_length=frame_len, fec=bool(alists),
                                             fec_codes=tuple(zip(names, alists)), mcs=mcs, initial_mcs_id=initial_mcs, **kw)

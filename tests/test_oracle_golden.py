@@ -154,3 +154,63 @@ def test_equalizer_qa_scenario():
         dec = [int(po.decide(c, hard[i:i + 1])[0]) if hard[i] != 0 else -1 for i in range(32)]
         assert dec == tx_data
         assert (res["fb_cnst"], res["fb_fec"]) == (po.BPSK, 0)      # :162-165 feedback {constellation: 1, fec: 0}
+
+
+# ---- python/dtl/qa_ofdm_adaptive_fec.py:60-61,71-171 ------------------------------------------------------------------
+# The reference's own FEC round trip: fec_frame_bvb -> frame_to_stream -> chunks_to_symbols -> soft_cf -> fec_decoder with
+# BOTH n=100 codes in one encoder / decoder list, fec id 1 and 2, frame_len 3 and 10 x 48 carriers, BPSK..16QAM, NO noise
+# tag (soft_cf's default sigma 0.001, soft_cf_impl.cc:89: the LLRs saturate to +-inf and every codeword leaves awgn_bp at
+# the initial hard-decision syndrome check), int(k * 69.69) input items, decoded output == input.
+# What is restated and what is not: the qa feeds one random BIT per input item and compares the flat lists; the framer in
+# the tree consumes BYTES through pdu_consumer (fec_frame_bvb_impl.cc:381-391), so the same items travel here as bytes of
+# value 0/1 and come back as bytes (fec_decoder's unpacked bits re-packed LSB first by fec_pack_bb).  The reference
+# framer is paced by its input queue; this repo's framer starts a TB only on a whole TB payload, so
+# the tail of the input that is shorter than one TB payload stays unsent -- asserted below instead of hidden.
+QA_FEC_CODES = [ALIST_100_23, ALIST_100_27]
+
+
+def qa_fec_geometry(cfg, cnst, fec):
+    """(payload bytes per TB, frames needed for n_items input bytes) as fec_frame_bvb_impl.cc:355-370 computes them"""
+    info = cfg.code_info(fec)
+    bps = po.bps(cnst)
+    frame_bytes = cfg.capacity * bps // 8
+    ncws = 1 + frame_bytes * 8 // info["N"] if frame_bytes * 8 > info["N"] else 1
+    pay = ncws * info["K"] // 8 - 4
+    tb_bits = 8 * ((ncws * (info["N"] - info["K"]) + (pay + 4) * 8 + 7) // 8)
+    return pay, tb_bits, frame_bytes * 8
+
+
+def qa_fec_input(cfg, fec, seed):
+    k = cfg.code_info(fec)["K"]
+    return np.random.default_rng(seed).integers(0, 2, int(k * 69.69)).astype(np.uint8)   # qa :76
+
+
+@pytest.mark.parametrize("frame_len", [3, 10])
+@pytest.mark.parametrize("fec", [1, 2])
+@pytest.mark.parametrize("cnst", [po.BPSK, po.QPSK, po.PSK8, po.QAM16])
+def test_fec_chain_qa_scenario(cnst, fec, frame_len):
+    cfg = po.Config(fft_len=64, frame_len=frame_len, alists=QA_FEC_CODES)
+    assert cfg.capacity == frame_len * 48                       # qa: frame_len * ofdm_sym_capacity
+    data = qa_fec_input(cfg, fec, 7 * cnst + fec)
+    pay, tb_bits, frame_bits = qa_fec_geometry(cfg, cnst, fec)
+    assert pay >= 1
+    n_tbs = data.size // pay
+    F = (n_tbs * (tb_bits + 8) + frame_bits - 1) // frame_bits + 2
+    fr = cfg.frame_batch(data[None, :], np.full(F, cnst, np.int32), np.full(F, fec, np.int32), 1, F)
+    assert fr["consumed"][0] == n_tbs * pay and fr["started"][0] == n_tbs
+    assert data.size - fr["consumed"][0] < pay                 # only the tail shorter than one TB payload is unsent
+    dec = po.FecDecoder(cfg)
+    b = po.bps(cnst)
+    out, n_ok, nit = [], 0, 0
+    for j in range(F):
+        m = fr["meta"][j]
+        syms = po.map_chunks(cnst, fr["chunks"][j])             # chunks_to_symbols_bc
+        llr = po.soft_dec(cnst, syms, 0.001)                    # soft_cf without a noise tag (:89)
+        assert np.all(np.isinf(llr[:m["packet_len"] * b]))
+        by, tbs = dec.frame(llr, m)
+        out.append(by)
+        n_ok += int(tbs["crc_ok"].sum())
+        nit += int(tbs["avg_it"].sum())
+    out = np.concatenate(out)
+    assert n_ok == n_tbs and nit == 0                           # every TB passes its CRC-32, no BP iteration ran
+    assert np.array_equal(out, data[:n_tbs * pay])              # qa :140-141
