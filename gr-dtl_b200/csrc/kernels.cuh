@@ -151,6 +151,14 @@ cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int byte
 } // namespace dtl
 
 #ifdef __CUDACC__
+// opt-in dynamic shared memory of kernel `k` on the current device: everything the SM allows beyond the kernel's static part
+template <class K> static inline cudaError_t set_max_dyn_smem(K k)
+{
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, k);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM - (int)a.sharedSizeBytes);
+}
 // 8-point forward DFT in registers (radix-2 then two radix-4), used by the 64-point FFT (8 x 8) in kernels_fft.cu and by
 // the equaliser kernel when the FFT is fused into it.
 __device__ __forceinline__ void dft8_fwd(float2 (&x)[8])

@@ -1035,10 +1035,9 @@ __global__ void cursor_clear_kernel(int* c) { *c = 0; }
 // Function attributes are per device: dtl_b200_create calls this after cudaSetDevice for every handle.
 cudaError_t init_kernels_fec()
 {
-    const int mx = DTL_MAX_DYN_SMEM;
-    cudaError_t e = cudaFuncSetAttribute(ldpc_screen_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ldpc_bp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(ldpc_plain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e = set_max_dyn_smem(ldpc_screen_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_plain_kernel);
     return e;
 }
 

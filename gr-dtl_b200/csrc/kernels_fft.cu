@@ -269,9 +269,9 @@ cudaError_t launch_tx_mod(cudaStream_t st, const TxParams& p)
 
 cudaError_t init_kernels_fft()
 {
-    cudaError_t e = cudaFuncSetAttribute(fft_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(fft_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tx_mod_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
+    cudaError_t e = set_max_dyn_smem(fft_fwd_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(fft_inv_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(tx_mod_kernel);
     return e;
 }
 

@@ -238,7 +238,7 @@ cudaError_t launch_header(cudaStream_t st, const HdrParams& p)
 
 cudaError_t init_kernels_hdr()
 {
-    return cudaFuncSetAttribute(header_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DTL_MAX_DYN_SMEM);
+    return set_max_dyn_smem(header_kernel);
 }
 
 } // namespace dtl

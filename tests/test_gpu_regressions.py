@@ -1,0 +1,60 @@
+"""Regression tests for defects found by review."""
+import numpy as np
+import pytest
+
+import pyoracle as orc
+from common import ALIST_300, make_oracle_cfg, make_receiver
+
+pytestmark = pytest.mark.gpu
+
+
+def test_no_fec_host_pipelined_results_wait_for_the_side_stream():
+    """fec_enabled = 0, DTL_MEM_HOST, >= 8 streams and >= 16 MB of input: rx_host_pipelined copies `res` out per chunk.  The
+    feedback fields are written by stream_state_kernel on the side stream; the no-FEC branch has to join it first."""
+    ocfg = make_oracle_cfg()
+    rx = make_receiver()
+    S, F = 16, 80                                      # 16 x 80 x 1840 x 8 B = 18.8 MB -> chunked path
+    assert S * F * rx.frame_samples * 8 >= 16 << 20
+    rng = np.random.default_rng(2)
+    cpf = rng.integers(1, 5, size=S * F).astype(np.int32)
+    t = ocfg.tx_batch(S, F, seed=77, cnst=1, snr_db=26.0, cnst_per_frame=cpf)
+    ref = ocfg.rx_batch(t["iq"], t["taps"], t["meta"], S, F, want_llr=False, want_syms=False)
+    for rep in range(3):                               # a race does not show every time
+        rx.reset(S)
+        got = rx.rx(t["iq"], t["taps"], t["meta"], S, F)
+        for k in ("fb_cnst", "fb_fec", "emitted", "lost_frames"):
+            assert np.array_equal(got["res"][k], ref["res"][k]), (k, rep)
+        assert np.allclose(got["res"]["snr_db"], ref["res"]["snr_db"], rtol=1e-4)
+        assert np.array_equal(got["frame_crc"], ref["frame_crc"])
+        for s in range(S):
+            assert np.array_equal(got["bytes"][s, :got["nbytes"][s]], ref["bytes"][s])
+    assert len(set(ref["res"]["fb_cnst"])) > 1, "feedback never moved: vacuous"
+    rx.close()
+
+
+@pytest.mark.parametrize("fec", [False, True])
+def test_mcs_stays_at_zero_when_the_estimate_is_below_every_threshold(fec):
+    """SNR estimate <= 0 dB at MCS 0 for more than decision_th frames (a link in a deep fade): the reference only asserts
+    current_mcs_id > 0 (ofdm_adaptive_feedback_decision.cc:70); here the MCS stays at 0 (no out-of-bounds table reads), and
+    recovers when the SNR comes back."""
+    al = (ALIST_300,) if fec else ()
+    ocfg = make_oracle_cfg(alists=al)
+    rx = make_receiver(alists=al)
+    S, F = 3, 10
+    bad = ocfg.tx_batch(S, F, seed=5, cnst=orc.BPSK, fec_id=1 if fec else 0, snr_db=-4.0)
+    good = ocfg.tx_batch(S, F, seed=6, cnst=orc.BPSK, fec_id=1 if fec else 0, snr_db=20.0)
+    for k in ("frame_no",):
+        good["meta"][k] = (good["meta"][k] + F) % 4096
+    iq = np.concatenate([bad["iq"].reshape(S, F, -1), good["iq"].reshape(S, F, -1)], axis=1).reshape(2 * S * F, -1)
+    taps = np.concatenate([bad["taps"].reshape(S, F, -1), good["taps"].reshape(S, F, -1)], axis=1).reshape(2 * S * F, -1)
+    meta = np.concatenate([bad["meta"].reshape(S, F), good["meta"].reshape(S, F)], axis=1).reshape(-1)
+    if fec:                                            # tag bookkeeping of the second half starts a new TB sequence
+        meta["tb_no"][np.arange(2 * S * F) % (2 * F) >= F] += 100
+    ref = ocfg.rx_batch(iq, taps, meta, S, 2 * F)
+    got = rx.rx(iq, taps, meta, S, 2 * F)
+    assert (ref["res"]["snr_db"].reshape(S, 2 * F)[:, :F] < 0).all()
+    for k in ("fb_cnst", "fb_fec", "lost_frames"):
+        assert np.array_equal(got["res"][k], ref["res"][k]), k
+    fb = got["res"]["fb_cnst"].reshape(S, 2 * F)
+    assert (fb[:, :F] == orc.BPSK).all() and (fb[:, -1] == orc.QPSK).all()
+    rx.close()

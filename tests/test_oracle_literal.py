@@ -25,7 +25,7 @@ CASES = [
     ("config1_nofec_8psk", dict(), 3, 20.0, 4, 8),
     ("config2_fec_qpsk", dict(alists=(ALIST_300,), initial_mcs=1, lut="config_fec"), 2, 17.0, 4, 8),
     ("config2_fec_16qam", dict(alists=(ALIST_300,), initial_mcs=1, lut="config_fec"), 4, 22.0, 4, 8),
-    ("config3_bpsk", dict(cnsts=ALL, alists=(ALIST_300,)), 1, 8.0, 4, 8),
+    ("config3_bpsk", dict(cnsts=ALL, alists=(ALIST_300,)), 1, 12.0, 4, 8),
     ("config3_64qam", dict(cnsts=ALL, alists=(ALIST_300,)), 5, 30.0, 4, 8),
     ("config3_256qam", dict(cnsts=ALL, alists=(ALIST_300,)), 6, 34.0, 4, 8),
     ("config4_16qam_ldpc", dict(alists=(ALIST_300,), initial_mcs=3), 4, 22.0, 6, 8),
@@ -119,6 +119,7 @@ def test_cuda_path_vs_reference_literal_mode(name, kw, cnst, snr, S, F):
             worst = max(worst, _rel(got["taps"][f], lit.work(freq[f].reshape(-1), t["taps"][f], t["meta"][f])[4]))
     assert worst <= TOL["taps"]
     # whole path from the same frequency-domain frames: bytes, CRC flags, TB records
+    rx.reset(S)                                                     # a fresh set of receivers, as the oracle's call
     full = rx.rx(freq, t["taps"], t["meta"], S, F, freq_domain=True)
     g = dict(res=full["res"], frame_crc=full["frame_crc"],
              bytes=[full["bytes"][s, :full["nbytes"][s]] for s in range(S)],
