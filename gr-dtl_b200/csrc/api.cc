@@ -39,7 +39,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
+    SL_CWBUF, SL_BPITEMS, SL_SGN, SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
     SL_TXDATA, SL_TXLEN, SL_TXCNST, SL_TXFEC, SL_TXTBS, SL_TXNTB, SL_TXKEEP, SL_TXSEGS, SL_TXCRC, SL_TXBITS, SL_TXCHUNKS, SL_TXMETA, SL_TXCONS, SL_TXSTARTED, SL_COUNT
 };
 
@@ -68,10 +68,13 @@ struct dtl_b200 {
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
     HdrDev hd{}; bool have_hdr = false;   // header branch tables (need the sync words)
+    int fast_tab_bytes = 0, fast_warp_bytes = 0; bool all_fast = true;   // reference-mode decoder, row-major layout (bp_ref.cuh)
+    const double2* d_exp_tab = nullptr;
     int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, max_n = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
     // per-stream state
     int n_streams = 0;
-    DevBuf st_buf, carry_buf, pend_buf;
+    DevBuf st_buf, carry_buf, pend_buf, csgn_buf;   // csgn: sign words of the carry buffer (screening pass)
+    int sgn_stride = 0, csgn_stride = 0;
     DevBuf txst_buf, txcarry_buf; int tx_streams = -1;   // TX FEC framer state (allocated by its first call)
     int carry_cap = 0;
     int* d_err = nullptr; int* d_cnt = nullptr; unsigned long long* d_bits_used = nullptr; int* d_cursor = nullptr;
@@ -88,6 +91,7 @@ struct dtl_b200 {
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr, ev_hdr = nullptr;
     bool side_pending = false, hdr_pending = false;
+    bool no_fast_bp = false;          // DTL_BP_OLD=1: the first (slot-major) reference-mode decoder, for A/B runs
     const float2* fuse_iq = nullptr;  // set by rx_device for one dev_equalize call: FFT fused into the equaliser kernel   // hdr_pending: the header branch of this call runs on the side stream
     int overlap = -1;
 
@@ -132,6 +136,70 @@ float2 expj_contract(double phase)
 
 int tb_ncws_host(int cw_len, int frame_len) { return frame_len > cw_len ? 1 + frame_len / cw_len : 1; }
 
+// sigma^2 as lr_of_rx (kernels_fec.cu) takes it: a power of two in a safe exponent range is passed as -(1/sigma^2)
+double sigma2_for_lr(double s2)
+{
+    int ex = 0;
+    const double m = std::frexp(s2, &ex);
+    return (m == 0.5 && ex > -500 && ex < 500) ? -(1.0 / s2) : s2;
+}
+
+// Assignment of the variables to (round, lane) positions of the decoder's column pass (bp_ref.cuh: var_pass).  The pass is
+// a flooding update -- every variable is independent -- so any assignment gives the same messages; the one chosen keeps the
+// 8-byte shared-memory accesses of a half warp (16 lanes, 16 bank pairs) on distinct banks wherever the graph allows:
+// lane's j-th access goes to slot[v][j], bank pair = slot % 16.  Greedy fill of the half-warp groups with the variable that
+// collides least with what the group already holds, a few hundred seeded restarts, best total kept.  Returns the order
+// (position -> variable, -1 = idle) and the wavefronts beyond one per access it leaves (0 = conflict-free).
+std::vector<int> order_variables(const std::vector<std::vector<int>>& slots, int n, int nvr, int cmax, int dummy, int* extra_out)
+{
+    const int groups = nvr * 2;
+    auto cost_of = [&](const std::vector<int>& ord) {
+        int extra = 0;
+        for (int g = 0; g < groups; g++)
+            for (int j = 0; j < cmax; j++) {
+                int cnt[16] = { 0 }, mx = 1;
+                for (int l = 0; l < 16; l++) {
+                    const int v = ord[g * 16 + l];
+                    if (v < 0 || j >= (int)slots[v].size()) continue;       // dummy slot: one address, a broadcast
+                    mx = std::max(mx, ++cnt[slots[v][j] & 15]);
+                }
+                extra += mx - 1;
+            }
+        return extra;
+    };
+    std::vector<int> best(groups * 16, -1);
+    for (int v = 0; v < n; v++) best[v] = v;
+    int best_cost = cost_of(best);
+    uint64_t rng = 0x9e3779b97f4a7c15ull;
+    auto next = [&]() { rng ^= rng << 13; rng ^= rng >> 7; rng ^= rng << 17; return rng; };
+    for (int attempt = 0; attempt < 400 && best_cost > 0; attempt++) {
+        std::vector<int> pool(n), ord(groups * 16, -1);
+        for (int v = 0; v < n; v++) pool[v] = v;
+        for (int i = n - 1; i > 0; i--) std::swap(pool[i], pool[next() % (uint64_t)(i + 1)]);
+        for (int g = 0; g < groups && !pool.empty(); g++) {
+            int cnt[4][16] = { { 0 } };
+            for (int l = 0; l < 16 && !pool.empty(); l++) {
+                int pick = 0, pick_c = 1 << 30;
+                for (size_t q = 0; q < pool.size() && pick_c > 0; q++) {
+                    const int v = pool[q];
+                    int c = 0;
+                    for (int j = 0; j < (int)slots[v].size() && j < 4; j++) c += cnt[j][slots[v][j] & 15];
+                    if (c < pick_c) { pick_c = c; pick = (int)q; }
+                }
+                const int v = pool[pick];
+                pool[pick] = pool.back(); pool.pop_back();
+                ord[g * 16 + l] = v;
+                for (int j = 0; j < (int)slots[v].size() && j < 4; j++) cnt[j][slots[v][j] & 15]++;
+            }
+        }
+        const int c = cost_of(ord);
+        if (c < best_cost) { best_cost = c; best = ord; }
+    }
+    (void)dummy;
+    if (extra_out) *extra_out = best_cost;
+    return best;
+}
+
 } // namespace
 
 // ---- lifecycle ---------------------------------------------------------------------------------------------------
@@ -153,7 +221,7 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
-    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->txst_buf.release(); h->txcarry_buf.release();
+    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->csgn_buf.release(); h->txst_buf.release(); h->txcarry_buf.release();
     h->prof.release();
     for (int i = 0; i < 2; i++) {
         if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
@@ -471,6 +539,38 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         d.row_wire = h->upload(row_wire, e);
         h->screen_tab_bytes += (2 * (code.m + slots) + 15) & ~15;
         d.pmat = h->upload(pmat, e); d.kwords = kwords;
+        {   // row-major tables of the reference-mode decoder (bp_ref.cuh)
+            const int rs = (code.max_row + 1) & ~1, nvr = (code.n + 31) / 32, dummy = code.m * rs;
+            d.rs = rs; d.nvr = nvr; d.uniform_rows = 1;
+            for (int r = 0; r < code.m; r++) if ((int)code.mlist[r].size() != code.max_row) d.uniform_rows = 0;
+            d.fast = bp_ref_has_instance(code.max_row, code.max_col) && dummy + 1 <= 65535 && code.n + 2 <= 65535;
+            if (d.fast) {
+                std::vector<uint16_t> rv2((size_t)code.m * 8, (uint16_t)code.n);
+                std::vector<std::vector<int>> vslots(code.n);
+                for (int r = 0; r < code.m; r++)
+                    for (size_t j = 0; j < code.mlist[r].size(); j++) rv2[(size_t)r * 8 + j] = (uint16_t)code.mlist[r][j];
+                for (int v = 0; v < code.n; v++)
+                    for (int r : code.nlist[v]) {
+                        int pos = 0;
+                        for (size_t q = 0; q < code.mlist[r].size(); q++) if (code.mlist[r][q] == v) pos = (int)q;
+                        vslots[v].push_back(r * rs + pos);
+                    }
+                int extra = 0;
+                const std::vector<int> ord = order_variables(vslots, code.n, nvr, code.max_col, dummy, &extra);
+                code.bank_extra = extra;
+                std::vector<uint32_t> vdesc((size_t)nvr * 32 * 4, 0u);
+                for (int i = 0; i < nvr * 32; i++) {
+                    const int v = ord[i];
+                    uint32_t sl[4] = { (uint32_t)dummy, (uint32_t)dummy, (uint32_t)dummy, (uint32_t)dummy };
+                    if (v >= 0) for (size_t j = 0; j < vslots[v].size(); j++) sl[j] = (uint32_t)vslots[v][j];
+                    vdesc[(size_t)i * 4] = sl[0] | (sl[1] << 16); vdesc[(size_t)i * 4 + 1] = sl[2] | (sl[3] << 16);
+                    vdesc[(size_t)i * 4 + 2] = v >= 0 ? (uint32_t)v : (uint32_t)(code.n + 1);
+                }
+                d.rv2 = (const uint4*)h->upload(rv2, e); d.vdesc = (const uint4*)h->upload(vdesc, e);
+                h->fast_tab_bytes += (int)fast_tab_bytes(code.n, code.m, nvr);
+                h->fast_warp_bytes = std::max(h->fast_warp_bytes, (int)fast_warp_bytes(code.n, code.m, rs));
+            } else h->all_fast = false;
+        }
         cd.push_back(d);
         max_n = std::max(max_n, code.n); h->max_k = std::max(h->max_k, code.k);
         h->warp_bytes = std::max(h->warp_bytes, (int)ldpc_warp_bytes(code.n, slots));
@@ -482,6 +582,11 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         h->codes.push_back(std::move(code));
     }
     h->d_codes = h->upload(cd, e);
+    {
+        std::vector<double> et;
+        exp_table(et);
+        h->d_exp_tab = (const double2*)h->upload(et, e);
+    }
     if (max_n) {
         h->max_n = max_n;
         h->max_ncws = tb_ncws_host(max_n, h->cap * h->max_bps);       // fec_decoder_impl.cc:54-72
@@ -533,7 +638,9 @@ extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
     h->n_mcs = c->n_mcs; h->initial_mcs = c->initial_mcs; h->decision_th = c->decision_th; h->hysteresis = c->hysteresis;
     dtl_status s = build_tables(h, c);
     if (s != DTL_OK) return bail(s);
+    { const char* ev = getenv("DTL_BP_OLD"); h->no_fast_bp = ev && atoi(ev); }
     h->llr_stride = h->cap * h->max_bps;
+    h->sgn_stride = (h->llr_stride + 31) / 32 + 1;
     h->bytes_stride = (((h->cap * h->max_bps + 7) / 8) + 3) & ~3;
     h->frame_samples = (h->L + h->H + 2) * (h->N + h->cp);
     void* p = nullptr;
@@ -557,9 +664,11 @@ extern "C" dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams)
     const size_t st_bytes = std::max<size_t>((size_t)n_streams * sizeof(StreamState), 16);
     const size_t carry_bytes = h->carry_cap ? (size_t)n_streams * h->carry_cap * sizeof(float) + 16 : 0;
     const size_t pend_bytes = (size_t)n_streams * sizeof(TbDesc) + 16;
-    if (st_bytes > h->st_buf.cap || carry_bytes > h->carry_buf.cap || pend_bytes > h->pend_buf.cap) CK(cudaStreamSynchronize(h->stream));
+    if (st_bytes > h->st_buf.cap || carry_bytes > h->carry_buf.cap || pend_bytes > h->pend_buf.cap ||
+        (carry_bytes && (size_t)n_streams * (h->carry_cap / 32 + 2) * 4 + 16 > h->csgn_buf.cap)) CK(cudaStreamSynchronize(h->stream));
     CK(h->st_buf.ensure(st_bytes));
     if (carry_bytes) CK(h->carry_buf.ensure(carry_bytes));
+    if (carry_bytes) { h->csgn_stride = h->carry_cap / 32 + 2; CK(h->csgn_buf.ensure((size_t)n_streams * h->csgn_stride * 4 + 16)); }
     CK(h->pend_buf.ensure(pend_bytes));
     CK(launch_stream_reset(h->stream, (StreamState*)h->st_buf.p, n_streams, h->initial_mcs));
     h->launches += n_streams > 0 ? 1 : 0;
@@ -737,7 +846,7 @@ dtl_status dev_demod(dtl_b200* h, const float2* iq, long long n_frames, float2* 
 
 dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2* taps, const dtl_frame_meta* meta, int S, int F,
                         float2* out_hard, float2* out_soft, float2* taps_out, dtl_frame_result* res,
-                        float* llr, int* n_llr, uint8_t* fbytes, int* fnbytes, int* fcrc)
+                        float* llr, int* n_llr, uint8_t* fbytes, int* fnbytes, int* fcrc, uint32_t* sgn = nullptr)
 {
     const long long n = (long long)S * F;
     if (!res) res = sg.scratch<dtl_frame_result>(SL_RES, (size_t)n);
@@ -747,6 +856,7 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     p.pl = h->pl; p.cn = h->cn; p.freq = freq; p.taps = taps; p.meta = meta; p.n_frames = n;
     p.out_hard = out_hard; p.out_soft = out_soft; p.taps_out = taps_out; p.res = res;
     p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr;
+    p.sgn = sgn; p.sgn_stride = h->sgn_stride;
     p.bytes = fbytes; p.bytes_stride = h->bytes_stride; p.nbytes = fnbytes; p.crc_ok = fcrc;
     p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
     if (h->fuse_iq) {
@@ -761,6 +871,10 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     if (h->hdr_pending) { h->hdr_pending = false; CK(cudaStreamWaitEvent(h->stream, h->ev_hdr, 0)); }   // tags + taps come from the side stream
     h->prof.begin(DTL_STAGE_EQ, 1);
     CK(launch_eq(h->stream, p, &eq_launches, ov ? &tags_due : nullptr));
+    if (sgn && !eq_emits_signs(p)) {             // the general kernel / tiny FFTs: sign words by a pass over the LLRs
+        CK(launch_llr_sign(h->stream, llr, h->llr_stride, n, sgn, h->sgn_stride));
+        eq_launches++;
+    }
     h->prof.end();
     cudaStream_t ss = h->stream;
     if (ov) {                                   // SNR tags and the per-stream feedback state: nothing on the main stream waits for them
@@ -782,13 +896,16 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
 }
 
 dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, const dtl_frame_meta* meta, int S, int F,
-                       uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs, FecParams& p)
+                       uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs, FecParams& p,
+                       const uint32_t* sgn = nullptr, int sgn_stride = 0)
 {
     if (h->codes.size() < 2) return fail(h, DTL_ERR_INVALID_ARG, "Misconfiguration: decoder not found!");
     memset(&p, 0, sizeof p);
     const size_t tb_slots = 2 * (size_t)F + 1, budget = (size_t)S * ((size_t)F + 2);
     p.st = (StreamState*)h->st_buf.p + h->s_off; p.n_streams = S; p.F = F; p.meta = meta; p.llr = llr; p.llr_stride = llr_stride;
     p.carry = (float*)h->carry_buf.p + (size_t)h->s_off * h->carry_cap; p.carry_cap = h->carry_cap;
+    p.sgn = sgn; p.sgn_stride = sgn_stride;
+    p.csgn = sgn ? (uint32_t*)h->csgn_buf.p + (size_t)h->s_off * h->csgn_stride : nullptr; p.csgn_stride = h->csgn_stride;
     p.n_codes = (int)h->codes.size() - 1; p.codes = h->d_codes; p.cap = h->cap;
     for (int c = 0; c <= DTL_CNST_MAX; c++) p.bps_tab[c] = cnst_bps(c);
     p.max_tb = h->max_tb;
@@ -817,6 +934,15 @@ dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride,
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");
     p.cnt = h->d_cnt; p.bits_used = h->d_bits_used;
     p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode; p.warp_bytes = h->warp_bytes;
+    p.fast = h->ldpc_mode == DTL_LDPC_REFERENCE && h->all_fast && !h->no_fast_bp;
+    p.fast_tab_bytes = h->fast_tab_bytes; p.fast_warp_bytes = h->fast_warp_bytes; p.exp_tab = h->d_exp_tab;
+    p.sigma2_lr = sigma2_for_lr(h->sigma2);
+    if (p.fast) {
+        p.cw_stride = (h->max_n + 3) & ~3;           // 16-byte multiples: one bulk copy per codeword
+        p.cwbuf = sg.scratch<float>(SL_CWBUF, (size_t)p.cw_cap * p.cw_stride);
+        p.items = sg.scratch<BpItem>(SL_BPITEMS, (size_t)p.cw_cap);
+        if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");
+    }
     p.bytes = bytes; p.bytes_cap = bytes_cap; p.nbytes = nbytes; p.tb_out = tbs; p.tb_cap = tb_cap; p.ntbs = ntbs;
     p.crc_table = h->crc_table; p.err = h->d_err;
     return DTL_OK;
@@ -826,9 +952,15 @@ dtl_status dev_fec(dtl_b200* h, Stage& sg, const float* llr, int llr_stride, con
                    uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs)
 {
     FecParams p;
-    dtl_status s = fec_prepare(h, sg, llr, llr_stride, meta, S, F, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, p);
+    const int sstride = (llr_stride + 31) / 32 + 1;
+    uint32_t* sgn = sg.scratch<uint32_t>(SL_SGN, (size_t)S * F * sstride + 4);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");
+    dtl_status s = fec_prepare(h, sg, llr, llr_stride, meta, S, F, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, p, sgn, sstride);
     if (s != DTL_OK) return s;
-    int launches = 0;
+    int launches = 1;
+    h->prof.begin(DTL_STAGE_LDPC, 1);
+    CK(launch_llr_sign(h->stream, llr, llr_stride, (long long)S * F, sgn, sstride));
+    h->prof.end();
     CK(launch_fec(h->stream, p, h->sm_count, &launches, &h->prof));
     h->launches += launches;
     return DTL_OK;
@@ -986,6 +1118,9 @@ extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const fl
     p.code = c.dev; p.count = count; p.max_it = h->ldpc_max_it; p.sigma2 = h->sigma2; p.mode = h->ldpc_mode;
     p.cursor = h->d_cursor; p.warp_bytes = (int)ldpc_warp_bytes(c.n, c.max_row * c.m);
     p.tab_bytes = (int)ldpc_tab_bytes(c.n, c.m, c.max_row * c.m, c.edges);
+    p.fast = h->ldpc_mode == DTL_LDPC_REFERENCE && c.dev.fast && !h->no_fast_bp;
+    p.fast_tab_bytes = (int)fast_tab_bytes(c.n, c.m, c.dev.nvr); p.fast_warp_bytes = (int)fast_warp_bytes(c.n, c.m, c.dev.rs);
+    p.exp_tab = h->d_exp_tab; p.sigma2_lr = sigma2_for_lr(h->sigma2);
     p.llr = sg.in(SL_LLR, llr, (size_t)count * c.n);
     p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
     p.nit = sg.out(SL_NIT, nit, (size_t)count);
@@ -1029,11 +1164,13 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
     const bool ov = h->fec_enabled && side_on(h);
     FecParams fp;
     float* d_llr = nullptr;
+    uint32_t* d_sgn = nullptr;
     int launches = 0;
     if (h->fec_enabled) {
         d_llr = sg.scratch<float>(SL_LLR, n * h->llr_stride);
+        d_sgn = sg.scratch<uint32_t>(SL_SGN, n * h->sgn_stride + 4);
         if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-        if ((s = fec_prepare(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, fp)) != DTL_OK) return s;
+        if ((s = fec_prepare(h, sg, d_llr, h->llr_stride, d_meta, S, F, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, fp, d_sgn, h->sgn_stride)) != DTL_OK) return s;
         if (ov) {                               // TB planning reads the tags only: beside the FFT and the equaliser
             CK(cudaEventRecord(h->ev_fork, h->stream));
             CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
@@ -1056,7 +1193,7 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
     }
     if (h->fec_enabled) {
         if (fused) { h->fuse_iq = d_in; d_freq = nullptr; }
-        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr);
+        s = dev_equalize(h, sg, d_freq, d_taps, d_meta, S, F, nullptr, nullptr, nullptr, d_res, d_llr, nullptr, nullptr, nullptr, nullptr, d_sgn);
         if (s != DTL_OK) return s;
         if (ov) CK(cudaStreamWaitEvent(h->stream, h->ev_plan, 0));
         CK(launch_fec(h->stream, fp, h->sm_count, &launches, &h->prof, ov ? 2 : 0, ov ? h->side_stream : nullptr, ov ? h->ev_eq : nullptr));

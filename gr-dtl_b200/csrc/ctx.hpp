@@ -83,6 +83,14 @@ struct CodeDev {
     const uint16_t* row_wire;    // [max_row*m] WIRE position (inverse permutation) of slot's variable: screening pass
     const uint32_t* pmat;        // [rank][kwords] parity part of the systematic generator, bit j of row i = P[i][j]
     int kwords;                  // ceil(k / 32)
+    // reference-mode decoder, row-major layout (bp_ref.cuh): message of edge j of row r lives at r*rs + j
+    int fast;                    // 1: max_row <= 8 and max_col <= 4 -- the tables below exist
+    int rs;                      // row stride of the message array in doubles (max_row rounded up to even)
+    int uniform_rows;            // every row has exactly max_row edges
+    int nvr;                     // variable rounds: ceil(n / 32)
+    const uint4* rv2;            // [m] variables of the row's edges as 8 x u16 in mlist order (pad: n)
+    const uint4* vdesc;          // [nvr*32] one entry per (round, lane): x = slot0 | slot1 << 16, y = slot2 | slot3 << 16 in nlist
+                                 //   order (pad: the dummy slot m*rs, which holds 1.0), z = variable (idle lane: n + 1)
 };
 
 // Per-stream receiver state that survives between calls.
@@ -120,10 +128,12 @@ struct Code {                    // host copy
     std::vector<int> permute;
     std::vector<std::vector<uint8_t>> P;   // rank x k parity part (for the TX-side encoder)
     CodeDev dev{};
+    int bank_extra = 0;          // shared-memory wavefronts beyond one per access the variable order leaves (api.cc: order_variables)
     std::string path;
 };
 
 bool load_alist(const std::string& path, Code& c, std::string& err);
+void exp_table(std::vector<double>& tab);   // [128][2]: tail, scale bits (bp_ref.cuh)
 
 // Per-stage device timer (dtl_b200_profile / dtl_b200_stage_times): event pairs on the handle's stream.
 struct Prof {

@@ -15,6 +15,21 @@ cudaError_t init_kernels_fft();
 
 #define DTL_MAX_SMEM_CODES 5     // codes 1..4 get their graph tables staged in shared memory
 
+// reference-mode decoder, row-major layout (bp_ref.cuh): shared-memory bytes of one code's tables / of one warp's buffers, and
+// whether bp_ref_run has an instance for a code with these maximum degrees
+__host__ __device__ inline size_t fast_tab_bytes(int n, int m, int nvr)
+{
+    return 16 * (size_t)m + 16 * (size_t)nvr * 32 + ((2 * (size_t)n + 15) & ~(size_t)15);
+}
+__host__ __device__ inline size_t fast_warp_bytes(int n, int m, int rs)
+{
+    return ((size_t)m * rs + 2) * 8 + ((((size_t)n + 2) * 8 + 15) & ~(size_t)15) + (((size_t)n + 2 + 15) & ~(size_t)15);   // msg, lr0, est: 16-byte multiples (rs is even)
+}
+inline bool bp_ref_has_instance(int max_row, int max_col)
+{
+    return max_row >= 3 && max_row <= 8 && max_col >= 1 && max_col <= 4 && !(max_row == 3 && max_col > 3);
+}
+
 __host__ __device__ inline int log2n_of(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
 
 // ---- stage 5 ------------------------------------------------------------------------------------------
@@ -44,11 +59,15 @@ struct EqParams {
     const float2* tw;
     int use_tma;                                   // set by the launcher: source 16-byte aligned
     float* mag;                                    // [n_frames][npil_frame] scratch: |pilot_eq| (eq_fast_kernel -> snr_tags_kernel)
+    uint32_t* sgn; int sgn_stride;                 // [n_frames][sgn_stride] hard decisions of the LLR stream, bit p % 32 of word p / 32 =
+                                                   //   (llr[p] > 0): what the decoder's screening pass reads instead of the LLRs (or null)
     // fused CP strip + FFT (eq_fast_kernel, fft_len 64): time-domain frames instead of `freq`
     const float2* iq; long long iq_frame_stride; int iq_sym0, iq_sym_stride, iq_skip;
 };
 // true when launch_eq would run the lean kernel with the FFT fused in for these parameters (p.iq set, p.freq unused)
 bool eq_can_fuse_fft(const EqParams& p);
+// true when launch_eq would fill p.sgn for these parameters (the lean kernel, fft_len >= 32); otherwise the caller runs launch_llr_sign
+bool eq_emits_signs(const EqParams& p);
 
 // ---- per-stream sequential bookkeeping ------------------------------------------------------------------
 struct StreamParams {
@@ -57,11 +76,15 @@ struct StreamParams {
     int n_mcs; const double* mcs_snr; const int* mcs_cnst; const int* mcs_fec; double hysteresis; int decision_th;
 };
 
+struct BpItem { long long out_off; int it, fec_id, k_, pad; };   // where a queued codeword's bits go (bp_gather_kernel -> ldpc_bp_ref_kernel)
+
 // ---- stage 4 ------------------------------------------------------------------------------------------------
 struct FecParams {
     StreamState* st; int n_streams, F;
     const dtl_frame_meta* meta;
     const float* llr; int llr_stride;
+    const uint32_t* sgn; int sgn_stride;           // sign words of the LLR stream (EqParams::sgn / llr_sign_kernel), [S*F][sgn_stride]
+    uint32_t* csgn; int csgn_stride;               // the same for the carry buffer, [S][csgn_stride] (carry_save_kernel)
     float* carry; int carry_cap;                   // [S][carry_cap]
     int n_codes; const CodeDev* codes;             // [n_codes+1], entry 0 unused
     int cap; int bps_tab[DTL_CNST_MAX + 1];
@@ -83,6 +106,11 @@ struct FecParams {
     int screen_words;                              // ceil(max n / 32)
     int tab_bytes, screen_bytes, screen_tab_bytes; // shared-memory graph tables; per-warp bytes and table bytes of the screening pass
     int max_it; double sigma2; int mode; int warp_bytes;
+    // reference mode on codes bp_ref.cuh has an instance for (all codes of the handle): ldpc_bp_ref_kernel
+    int fast; int fast_tab_bytes, fast_warp_bytes; const double2* exp_tab;
+    double sigma2_lr;                              // sigma2, or -(1/sigma2) when sigma2 is a power of two (lr_of_rx)
+    float* cwbuf; int cw_stride;                   // [queued codewords][cw_stride] received values in H column order (bp_gather_kernel)
+    BpItem* items;                                 // [queued codewords]
     // outputs
     uint8_t* bytes; int bytes_cap; int* nbytes; dtl_tb_result* tb_out; int tb_cap; int* ntbs;
     const uint32_t* crc_table; int* err;
@@ -91,6 +119,7 @@ struct FecParams {
 struct LdpcParams {                                // stand-alone fec_dec::decode batches
     CodeDev code; const float* llr; long long count; uint8_t* bits; int* nit; int max_it; double sigma2; int mode;
     int* cursor; int warp_bytes; int tab_bytes;
+    int fast; int fast_tab_bytes, fast_warp_bytes; const double2* exp_tab; double sigma2_lr;
 };
 
 // ---- TX FEC framer --------------------------------------------------------------------------------
@@ -132,6 +161,8 @@ cudaError_t launch_eq(cudaStream_t st, const EqParams& p, int* launches = nullpt
 // tags_deferred != nullptr: the lean kernel's snr_tags_kernel is left to the caller (launch_snr_tags, any stream ordered
 // after `st`), *tags_deferred says whether one is due
 cudaError_t launch_snr_tags(cudaStream_t st, const EqParams& p);
+// sign words of n_frames rows of llr_stride floats: sgn[f][w] bit b = llr[f][32 w + b] > 0 (rows padded with zeros to sgn_stride words)
+cudaError_t launch_llr_sign(cudaStream_t st, const float* llr, int llr_stride, long long n_frames, uint32_t* sgn, int sgn_stride);
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);
 cudaError_t launch_stream_state(cudaStream_t st, const StreamParams& p);
 // phase 0: everything; 1: TB planning only (needs the tags, not the LLRs); 2: what follows the planning
@@ -151,6 +182,28 @@ cudaError_t launch_frame_gather(cudaStream_t st, const uint8_t* fbytes, int byte
 } // namespace dtl
 
 #ifdef __CUDACC__
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier helpers ------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase)
+{
+    asm volatile("{\n .reg .pred p;\nW: mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra D;\n bra W;\nD:\n}"
+                 ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+
 // opt-in dynamic shared memory of kernel `k` on the current device: everything the SM allows beyond the kernel's static part
 template <class K> static inline cudaError_t set_max_dyn_smem(K k)
 {

@@ -24,6 +24,7 @@
 // sum-product on likelihood ratios, IEEE double, products in alist order) so payload bits AND iteration
 // counts match the reference; DTL_LDPC_LAYERED is a layered normalised min-sum in fp32 (throughput mode).
 #include "kernels.cuh"
+#include "bp_ref.cuh"
 #include <cstdlib>
 
 namespace dtl {
@@ -314,30 +315,6 @@ __device__ __forceinline__ void bp_iter_generic(const CodeS& c, const WarpBuf& w
     __syncwarp();
 }
 
-// IEEE double division without the library routine's per-call reconvergence scaffolding.  ddiv_try() is __ddiv_rn's own
-// fast path, operation for operation (reciprocal seed MUFU.RCP64H with low word 1, two Newton steps, quotient, exact
-// remainder, one correction) and its own acceptance test (the quotient's high word, read as a float, is a normal
-// number and the divisor's is finite); ok == false means the library takes its slow path (zero / infinite / NaN /
-// subnormal operands or results), and the caller then calls __ddiv_rn itself.  The values are therefore the library's
-// in every case; what changes is that several independent divisions can be in flight per thread.
-__device__ __forceinline__ double ddiv_try(double a, double b, bool& ok)
-{
-    double seed;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(seed) : "d"(b));
-    const double r0 = __hiloint2double(__double2hiint(seed), 1);
-    double e = __fma_rn(-b, r0, 1.0);
-    e = __fma_rn(e, e, e);
-    const double r1 = __fma_rn(r0, e, r0);
-    const double e2 = __fma_rn(-b, r1, 1.0);
-    const double r2 = __fma_rn(r1, e2, r1);
-    const double q0 = __dmul_rn(a, r2);
-    const double rem = __fma_rn(-b, q0, a);
-    const double q = __fma_rn(r2, rem, q0);
-    const float chk = __fmaf_rn(0.0f, __int_as_float(__double2hiint(b)), __int_as_float(__double2hiint(q)));
-    ok = fabsf(chk) > 1.469367938527859385e-39f;
-    return q;
-}
-
 // The same iteration for row weight <= RMAX and column weight <= CMAX with the per-edge work unrolled, branch-free
 // and predicated: the divisions of a row (column) are independent instruction chains the scheduler interleaves, and
 // each t = 2/(1+Q) - 1 is computed once (identical value, identical roundings).
@@ -624,10 +601,49 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
     uint32_t* plane = estw + 32 * nwp;                                    // [32*screen_words + 1]
     for (int it0 = (blockIdx.x * warps + wid) * 32; it0 < total; it0 += gridDim.x * warps * 32) {
         const int cnt = min(32, total - it0);
-        // ---- descriptors of codeword it0 + lane
-        int my_fec = 0, my_k = 0, my_p0 = 0, my_p1 = 0, my_single = 1;
-        const float* my_src = nullptr;
+        int my_fec = 0, my_k = 0;
         long long my_out = 0;
+        if (p.sgn) {
+            // ---- hard decisions from the sign words the equaliser kernel wrote next to the LLRs (16 MB instead of the 508 MB
+            // of LLRs this pass used to read): lane l builds the row of codeword it0 + l on its own -- per segment that
+            // overlaps the codeword, 32 stream bits per word with one funnel shift, masked to the segment's range
+            uint32_t* row = estw + lane * nwp;
+            for (int w = 0; w < nwp; w++) row[w] = 0u;
+            if (lane < cnt) {
+                const int it = it0 + lane;
+                const TbDesc& d = p.tbs[p.cw_tb[it]];
+                my_fec = d.fec_id;
+                const ScreenCode sc = s_code[my_fec];
+                const int rcv_idx = p.cw_geo[3 * it], nw = (sc.n + 31) >> 5;
+                my_k = p.cw_geo[3 * it + 2];
+                my_out = d.bit_base + p.cw_geo[3 * it + 1];
+                const int len = (sc.n - sc.k) + my_k, nseg = d.nseg;
+                int base = 0;
+                for (int i = 0; i < nseg; i++) {
+                    const TbSeg sg = d.seg[i];
+                    const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+                    if (lo < hi) {
+                        const uint32_t* sw = sg.src < 0 ? p.csgn + (size_t)d.stream * p.csgn_stride
+                                                        : p.sgn + ((size_t)d.stream * p.F + sg.src) * p.sgn_stride;
+                        const int nwords = sg.src < 0 ? p.csgn_stride : p.sgn_stride;
+                        const int e0 = sg.start + (rcv_idx - base);          // stream index of codeword position 0
+                        const int p0 = lo - rcv_idx, p1 = hi - rcv_idx;
+                        for (int w = p0 >> 5; w < nw && 32 * w < p1; w++) {
+                            const int bitpos = e0 + 32 * w, wi = bitpos >> 5, sh = bitpos & 31;
+                            const uint32_t a = (wi >= 0 && wi < nwords) ? __ldg(&sw[wi]) : 0u;
+                            const uint32_t b = (wi + 1 >= 0 && wi + 1 < nwords) ? __ldg(&sw[wi + 1]) : 0u;
+                            const int l0 = max(p0 - 32 * w, 0), l1 = min(p1 - 32 * w, 32);
+                            const uint32_t m = (l1 >= 32 ? 0xffffffffu : (1u << l1) - 1u) & ~((1u << l0) - 1u);
+                            row[w] |= __funnelshift_r(a, b, sh) & m;
+                        }
+                    }
+                    base += sg.len;
+                }
+            }
+        } else {
+        // ---- descriptors of codeword it0 + lane
+        int my_p0 = 0, my_p1 = 0, my_single = 1;
+        const float* my_src = nullptr;
         if (lane < cnt) {
             const int it = it0 + lane;
             const TbDesc& d = p.tbs[p.cw_tb[it]];
@@ -652,8 +668,6 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
             }
             my_single = hits <= 1;
         }
-        const int fec0 = __shfl_sync(0xffffffffu, my_fec, 0);
-        const bool uniform = __all_sync(0xffffffffu, lane >= cnt || my_fec == fec0);
         // ---- hard decisions, one ballot word per 32 wire positions
         for (int l = 0; l < cnt; l++) {
             const int fec = __shfl_sync(0xffffffffu, my_fec, l);
@@ -703,6 +717,9 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
                 }
             }
         }
+        }
+        const int fec0 = __shfl_sync(0xffffffffu, my_fec, 0);
+        const bool uniform = __all_sync(0xffffffffu, lane >= cnt || my_fec == fec0);
         __syncwarp();
         // ---- syndromes
         unsigned badw = 0;
@@ -802,6 +819,180 @@ __global__ void __launch_bounds__(32 * DTL_BP_WARPS, DTL_BP_MINB) ldpc_bp_kernel
         uint8_t* out = p.bits + d.bit_base + d_idx;
         for (int q = lane; q < k_; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
         if (lane == 0) p.cw_nit[it] = nit;
+        __syncwarp();
+    }
+}
+
+
+// ---- reference mode, row-major layout (bp_ref.cuh) ------------------------------------------------------------------
+// Gather of one codeword straight into what awgn_bp starts from: lr0[col] = exp(-2 rx / sigma^2) with rx = -llr
+// (ldpc_dec.cc:64-66, rx_lr_calc) and est[col] = rx < 0 (compute_init_estimate); positions past the received length read
+// as LLR 0 (lr = exp(0) = 1), shortened positions as -15 (tb_decoder.cc:145,161-183).
+// sigma2 > 0: divide; sigma2 < 0: -sigma2 is an exact power of two and 1/sigma2 = -1/(-sigma2) is passed instead -- the quotient
+// by a power of two is the product by its reciprocal, bit for bit (the default sigma^2 = 2: one multiplication, no division)
+__device__ __forceinline__ double lr_of_rx(float x, double sigma2, const double2* __restrict__ T)
+{
+    const float m2 = -1 * 2 * x;
+    double q;
+    if (sigma2 < 0.0) q = __dmul_rn((double)m2, -sigma2);
+    else {
+        bool ok;
+        q = ddiv_try((double)m2, sigma2, ok);
+        if (__builtin_expect(!ok, 0)) q = __ddiv_rn((double)m2, sigma2);
+    }
+    return exp_tab(q, T);
+}
+
+// Gather of the queued codewords, one warp each, grid-stride: the n received values of the TB's receive buffer (reads past
+// the received length = 0, shortened positions = -15, tb_decoder.cc:145,161-183), negated and permuted into H column order
+// (ldpc_dec.cc:64-66), written as one contiguous block per queued codeword -- the decoder then fetches a codeword with ONE
+// bulk copy issued a whole decode ahead, instead of walking descriptors -> segments -> LLRs with every load waiting for the
+// one before it (profiles/r02a: a third of the decoder's warps sat in that chain at any time).
+__global__ void __launch_bounds__(256) bp_gather_kernel(FecParams p)
+{
+    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    const int n0 = p.cnt[3], n1 = n0 + p.cnt[5], n2 = n1 + p.cnt[6], total = n2 + p.cnt[7];
+    for (int j = blockIdx.x * warps + (threadIdx.x >> 5); j < total; j += gridDim.x * warps) {
+        const int it = j < n0 ? p.bp_list[j] : j < n1 ? p.bp_list[(size_t)p.cw_cap + (j - n0)]
+                     : j < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (j - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (j - n2)];
+        const TbDesc& d = p.tbs[p.cw_tb[it]];
+        const CodeDev& c = p.codes[d.fec_id];
+        const int n = c.n, rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - c.k) + k_;
+        float* dst = p.cwbuf + (size_t)j * p.cw_stride;
+        if (lane == 0) {
+            BpItem r;
+            r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_; r.pad = 0;
+            p.items[j] = r;
+        }
+        // wire order, coalesced: defaults first (positions past the received length read as LLR 0, shortened ones as -15), then
+        // every segment that overlaps the codeword copies its run; the column permutation is applied by the decoder when it
+        // turns the block into likelihood ratios (a shared-memory scatter there, a sector-wasting global one here)
+        for (int q = lane; q < p.cw_stride; q += 32) dst[q] = q < len ? -0.0f : 15.0f;      // -1 * 0 and -1 * -15
+        __syncwarp();
+        const int nseg = d.nseg;
+        int base = 0;
+        for (int i = 0; i < nseg; i++) {
+            const TbSeg sg = d.seg[i];
+            const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+            if (lo < hi) {
+                const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                              : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                for (int g = lo + lane; g < hi; g += 32) dst[g - rcv_idx] = -1 * __ldcs(&src[g - base]);
+            }
+            base += sg.len;
+        }
+    }
+}
+
+// bp_ref_run behind a call: the decoder's inner loops get a register allocation of their own, the kernel's per-codeword
+// state (queue index, item record, pointers) is saved around ONE call per codeword instead of competing with the
+// division chains for the 64 registers a thread has when 32 warps are resident
+template <int NT>
+__device__ __noinline__ int bp_ref_call(const FastS* cp, unsigned char* base, const unsigned char* smb, int tid, int max_it, int bar_id)
+{
+    FastS c = *cp;
+    c.smb = smb;
+    const FastBuf w = fast_carve(base, c.n, c.m, c.rs);
+    return bp_ref_run<NT>(c, w, tid, max_it, bar_id);
+}
+
+// Pass 2, reference mode: persistent, one codeword per TEAM of NT threads (NT / 32 warps behind a named barrier) from the
+// queue.  What bounds this kernel is how many warps the SM can choose from, not instruction count: one warp issues an FP64
+// instruction with three register-pair operands about every six cycles however many independent chains it holds (tools/
+// div_bench.cu, tools/bp_bench.cu on a B200), the FP64 pipe takes one every two, and the shared memory a codeword needs
+// (11 KB) caps the codewords in flight at ~19 per SM -- so two warps share a codeword's rows and columns (the same total
+// warp-rounds: 148 rows = 32+32+32+32+20, 300 columns = 9 x 32 + 12) and 64 registers per thread keep 32 warps resident.
+// Each team owns a staging buffer and an mbarrier; the block of the NEXT codeword is fetched by one bulk copy
+// (cp.async.bulk -> mbarrier) as soon as the current one has been turned into likelihood ratios.
+template <int NT, int TEAMS, int MINB>
+__global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ FastS scodes[DTL_MAX_SMEM_CODES];
+    __shared__ __align__(8) uint64_t bars[TEAMS];
+    __shared__ int s_next[TEAMS];
+    const int team = threadIdx.x / NT, tid = threadIdx.x - team * NT, bar_id = team + 1;
+    {
+        int off = 0;
+        for (int ci = 1; ci <= p.n_codes; ci++) {
+            const CodeDev g = p.codes[ci];
+            const FastS sc = stage_fast(g, sm, off);
+            if (threadIdx.x == 0) scodes[ci] = sc;
+            off += (int)fast_tab_bytes(g.n, g.m, g.nvr);
+        }
+        if (tid == 0) { mbar_init(&bars[team], 1); s_next[team] = atomicAdd(&p.cnt[1], 1); }
+        __syncthreads();
+    }
+    const int stg_bytes = p.cw_stride * 4;
+    unsigned char* base = sm + p.fast_tab_bytes + (size_t)team * (p.fast_warp_bytes + stg_bytes);
+    float* stg = (float*)(base + p.fast_warp_bytes);
+    uint64_t* bar = &bars[team];
+    const int total = p.cnt[3] + p.cnt[5] + p.cnt[6] + p.cnt[7];
+    int j = s_next[team];
+    BpItem rec;
+    rec.out_off = 0; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.pad = 0;
+    if (j < total) {
+        if (tid == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)j * p.cw_stride, (uint32_t)stg_bytes, bar); }
+        rec = p.items[j];
+    }
+    team_sync<NT>(bar_id);                                             // everybody has read s_next
+    uint32_t phase = 0;
+    while (j < total) {
+        if (tid == 0) s_next[team] = atomicAdd(&p.cnt[1], 1);         // its latency hides behind the likelihood-ratio pass
+        FastS c = scodes[rec.fec_id];
+        c.smb = sm;
+        const FastBuf w = fast_carve(base, c.n, c.m, c.rs);
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        for (int q = tid; q < c.n; q += NT) {                          // ldpc_dec.cc:64-66, rx_lr_calc, compute_init_estimate
+            const float x = stg[q];
+            const int col = c.permute()[q];
+            w.lr0[col] = lr_of_rx(x, p.sigma2_lr, p.exp_tab);
+            w.est[col] = x < 0.f ? 1 : 0;
+        }
+        team_sync<NT>(bar_id);
+        const int nxt = s_next[team];
+        BpItem nrec = rec;
+        if (nxt < total) {
+            if (tid == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)nxt * p.cw_stride, (uint32_t)stg_bytes, bar); }
+            nrec = p.items[nxt];
+        }
+        const int nit = NT == 32 ? bp_ref_run<NT>(c, w, tid, p.max_it, bar_id) : bp_ref_call<NT>(&scodes[rec.fec_id], base, sm, tid, p.max_it, bar_id);
+        uint8_t* out = p.bits + rec.out_off;
+        for (int q = tid; q < rec.k_; q += NT) out[q] = w.est[c.permute()[c.rank + q]];
+        if (tid == 0) p.cw_nit[rec.it] = nit;
+        team_sync<NT>(bar_id);
+        j = nxt; rec = nrec;
+    }
+}
+
+__global__ void __launch_bounds__(128, 4) ldpc_plain_ref_kernel(LdpcParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    FastS c = stage_fast(p.code, sm, 0);
+    c.smb = sm;
+    __syncthreads();
+    const FastBuf w = fast_carve(sm + p.fast_tab_bytes + (size_t)wid * p.fast_warp_bytes, c.n, c.m, c.rs);
+    if (lane == 0) w.est[c.n] = 0;
+    for (;;) {
+        long long it = 0;
+        if (lane == 0) it = atomicAdd(p.cursor, 1);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= p.count) break;
+        const float* in = p.llr + it * c.n;
+        for (int q = lane; q < c.n; q += 32) {                                      // ldpc_dec.cc:64-66
+            const float x = -1 * in[q];
+            const int col = c.permute()[q];
+            w.lr0[col] = lr_of_rx(x, p.sigma2_lr, p.exp_tab);
+            w.est[col] = x < 0.f ? 1 : 0;
+        }
+        __syncwarp();
+        int nit = 0;
+        if (syn_nonzero<8>(c, w.est, lane)) nit = bp_ref_run(c, w, lane, p.max_it);
+        uint8_t* out = p.bits + it * c.k;
+        for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
+        if (lane == 0 && p.nit) p.nit[it] = nit;
         __syncwarp();
     }
 }
@@ -977,6 +1168,15 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
         }                                      // src < 0: the carry segment is always first and already in place
         base += sg.len;
     }
+    if (p.csgn) {                              // the carry buffer's sign words for the next call's screening pass
+        __syncwarp();
+        uint32_t* cs = p.csgn + (size_t)s * p.csgn_stride;
+        for (int q0 = 0; q0 < base; q0 += 32) {
+            const bool bit = q0 + lane < base && carry[q0 + lane] > 0.f;
+            const unsigned word = __ballot_sync(0xffffffffu, bit);
+            if (lane == 0) cs[q0 >> 5] = word;
+        }
+    }
 }
 
 __global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used)
@@ -1005,7 +1205,25 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         if (!per_sm_screen) { const char* e = getenv("DTL_SCREEN_CTAS"); per_sm_screen = e && atoi(e) > 0 ? atoi(e) : 8; }
         ldpc_screen_kernel<<<sm_count * per_sm_screen, 256, smem, st>>>(p);
     }
-    {   // pass 2: belief propagation on what did not pass, persistent
+    if (p.fast) {   // pass 2, reference mode on codes with a row-major instance (bp_ref.cuh)
+        static int wsel = 0;                         // DTL_BP_TEAM=32|64: threads per codeword (A/B; 64 = two warps per codeword)
+        if (!wsel) { const char* e = getenv("DTL_BP_TEAM"); wsel = e && atoi(e) > 0 ? atoi(e) : 32; }
+        bp_gather_kernel<<<sm_count * 8, 256, 0, st>>>(p);
+        const size_t per_warp = (size_t)p.fast_warp_bytes + (size_t)p.cw_stride * 4;
+        auto launch = [&](auto kern, int teams, int threads, int max_ctas) {
+            const size_t sm_bytes = (size_t)p.fast_tab_bytes + per_warp * teams;
+            int per_sm = (int)((227 * 1024) / (sm_bytes + 1024 + 256));
+            if (per_sm < 1) per_sm = 1;
+            if (per_sm > max_ctas) per_sm = max_ctas;
+            if (sm_bytes + 256 > 227 * 1024) return cudaErrorInvalidConfiguration;
+            kern<<<sm_count * per_sm, threads, sm_bytes, st>>>(p);
+            return cudaSuccess;
+        };
+        cudaError_t le = wsel == 32 ? launch(ldpc_bp_ref_kernel<32, 6, 3>, 6, 192, 3) : launch(ldpc_bp_ref_kernel<64, 4, 4>, 4, 256, 4);
+        if (le != cudaSuccess) return le;
+        if (launches) *launches += 1;
+        prof->end();
+    } else {   // pass 2: belief propagation on what did not pass, persistent
         const int warps = DTL_BP_WARPS;
         const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
         if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
@@ -1038,6 +1256,9 @@ cudaError_t init_kernels_fec()
     cudaError_t e = set_max_dyn_smem(ldpc_screen_kernel);
     if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_kernel);
     if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_plain_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_ref_kernel<32, 6, 3>);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_ref_kernel<64, 4, 4>);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_plain_ref_kernel);
     return e;
 }
 
@@ -1053,7 +1274,11 @@ cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
     long long want = (p.count + warps - 1) / warps;
     int blocks = (int)(want < (long long)sm_count * per_sm ? want : (long long)sm_count * per_sm);
     cursor_clear_kernel<<<1, 1, 0, st>>>(p.cursor);
-    ldpc_plain_kernel<<<blocks, warps * 32, smem, st>>>(p);
+    if (p.fast) {
+        const size_t fsmem = (size_t)p.fast_tab_bytes + (size_t)p.fast_warp_bytes * warps;
+        if (fsmem > 227 * 1024) return cudaErrorInvalidConfiguration;
+        ldpc_plain_ref_kernel<<<blocks, warps * 32, fsmem, st>>>(p);
+    } else ldpc_plain_kernel<<<blocks, warps * 32, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -9,6 +9,7 @@
 #include "ctx.hpp"
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <fstream>
 #include <sstream>
 
@@ -61,6 +62,32 @@ void cnst_points(int c, std::vector<float2>& pts, std::vector<float2>& inv, floa
     for (auto& p : pts) {
         const double re = p.x, im = p.y, d = re * re + im * im;
         inv.push_back(make_float2((float)(re / d), (float)(-im / d)));
+    }
+}
+
+// Table of the decoder's exp() (bp_ref.cuh: exp_tab): for i in [0, 128) the pair (tail_i, bits_i) with 2^(i/128) = H_i (1 + tail_i),
+// H_i the nearest double, bits_i = the bit pattern of H_i minus (i << 45) stored in a double's 8 bytes -- the layout of the
+// table-driven exp of glibc >= 2.28 (sysdeps/ieee754/dbl-64/e_exp_data.c, N = 128).  Computed here in 113-bit arithmetic:
+// 2^(1/128) by seven square roots (Newton), powers by multiplication.
+void exp_table(std::vector<double>& tab)
+{
+    typedef __float128 q;
+    q step = 2;
+    for (int k = 0; k < 7; k++) {
+        q y = (q)std::sqrt((double)step);
+        for (int it = 0; it < 6; it++) y = (y + step / y) / 2;
+        step = y;
+    }
+    tab.assign(256, 0.0);
+    q t = 1;
+    for (int i = 0; i < 128; i++) {
+        const double hi = (double)t, tail = (double)((t - (q)hi) / (q)hi);   // relative: 2^(i/128) = H (1 + tail)
+        uint64_t bits;
+        memcpy(&bits, &hi, 8);
+        bits -= (uint64_t)i << 45;
+        tab[2 * i] = tail;
+        memcpy(&tab[2 * i + 1], &bits, 8);
+        t *= step;
     }
 }
 
