@@ -68,6 +68,7 @@ struct dtl_b200 {
     const int* d_tx_base = nullptr; const uint8_t* d_tx_pil_mask = nullptr; const float2* d_tx_pil_val = nullptr;
     int hdr_stride = 0;
     HdrDev hd{}; bool have_hdr = false;   // header branch tables (need the sync words)
+    int lay_tab_bytes = 0, lay_warp_bytes = 0; bool all_lay = true;         // layered decoder (bp_layered.cuh)
     int fast_tab_bytes = 0, fast_warp_bytes = 0; bool all_fast = true;   // reference-mode decoder, row-major layout (bp_ref.cuh)
     const double2* d_exp_tab = nullptr;
     int warp_bytes = 0, max_tb = 0, max_ncws = 1, max_k = 0, max_n = 0, tab_bytes = 0, screen_bytes = 16, screen_tab_bytes = 0, screen_words = 0;
@@ -142,6 +143,30 @@ double sigma2_for_lr(double s2)
     int ex = 0;
     const double m = std::frexp(s2, &ex);
     return (m == 0.5 && ex > -500 && ex < 500) ? -(1.0 / s2) : s2;
+}
+
+// Steps of the layered decoder (bp_layered.cuh): groups of check rows that share no variable, at most 32 rows each, one lane
+// per row.  Greedy colouring: rows in order, each into the first group that holds none of its variables and has a free
+// lane (13 groups for the n = 300 code).  Packing the rows into ceil(m / 32) full groups and resolving the few shared
+// variables with shared-memory atomic adds was measured slower (float atomics on shared memory are compare-and-swap loops).
+std::vector<std::vector<int>> schedule_rows(const std::vector<std::vector<int>>& mlist, int n, int* shared_out)
+{
+    std::vector<std::vector<int>> groups;
+    std::vector<std::vector<char>> used;
+    for (int r = 0; r < (int)mlist.size(); r++) {
+        int g = -1;
+        for (size_t k = 0; k < groups.size() && g < 0; k++) {
+            if (groups[k].size() >= 32) continue;
+            bool ok = true;
+            for (int v : mlist[r]) if (used[k][v]) { ok = false; break; }
+            if (ok) g = (int)k;
+        }
+        if (g < 0) { groups.emplace_back(); used.emplace_back(n, 0); g = (int)groups.size() - 1; }
+        groups[g].push_back(r);
+        for (int v : mlist[r]) used[g][v] = 1;
+    }
+    if (shared_out) *shared_out = 0;
+    return groups;
 }
 
 // Assignment of the variables to (round, lane) positions of the decoder's column pass (bp_ref.cuh: var_pass).  The pass is
@@ -544,6 +569,31 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
             d.rs = rs; d.nvr = nvr; d.uniform_rows = 1;
             for (int r = 0; r < code.m; r++) if ((int)code.mlist[r].size() != code.max_row) d.uniform_rows = 0;
             d.fast = bp_ref_has_instance(code.max_row, code.max_col) && dummy + 1 <= 65535 && code.n + 2 <= 65535;
+            const bool have_rv2 = code.max_row <= 7 && dummy + 1 <= 65535 && code.n + 2 <= 65535;
+            if (have_rv2) {                      // layered decoder: row groups (bp_layered.cuh)
+                const auto groups = schedule_rows(code.mlist, code.n, &code.lay_shared);
+                // one 16-byte descriptor per (step, lane): the row's variables (pad: n) and the row id (0xffff = idle lane)
+                std::vector<uint16_t> lrows(groups.size() * 32 * 8, (uint16_t)code.n);
+                for (size_t g = 0; g < groups.size(); g++)
+                    for (size_t l = 0; l < 32; l++) {
+                        uint16_t* ds = &lrows[(g * 32 + l) * 8];
+                        ds[7] = 0xffff;
+                        if (l < groups[g].size()) {
+                            const int r = groups[g][l];
+                            for (size_t j = 0; j < code.mlist[r].size() && j < 7; j++) ds[j] = (uint16_t)code.mlist[r][j];
+                            ds[7] = (uint16_t)r;
+                        }
+                    }
+                d.lay_steps = (int)groups.size(); d.lay_rows = h->upload(lrows, e);
+                h->lay_tab_bytes += (int)lay_tab_bytes(code.n, code.m, d.lay_steps);
+                h->lay_warp_bytes = std::max(h->lay_warp_bytes, (int)lay_warp_bytes(code.n, code.m, rs));
+            } else h->all_lay = false;
+            if (have_rv2 && !d.fast) {           // the layered decoder needs the row table even where the reference one has no instance
+                std::vector<uint16_t> rv2l((size_t)code.m * 8, (uint16_t)code.n);
+                for (int r = 0; r < code.m; r++)
+                    for (size_t j = 0; j < code.mlist[r].size(); j++) rv2l[(size_t)r * 8 + j] = (uint16_t)code.mlist[r][j];
+                d.rv2 = (const uint4*)h->upload(rv2l, e);
+            }
             if (d.fast) {
                 std::vector<uint16_t> rv2((size_t)code.m * 8, (uint16_t)code.n);
                 std::vector<std::vector<int>> vslots(code.n);
@@ -937,7 +987,9 @@ dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride,
     p.fast = h->ldpc_mode == DTL_LDPC_REFERENCE && h->all_fast && !h->no_fast_bp;
     p.fast_tab_bytes = h->fast_tab_bytes; p.fast_warp_bytes = h->fast_warp_bytes; p.exp_tab = h->d_exp_tab;
     p.sigma2_lr = sigma2_for_lr(h->sigma2);
-    if (p.fast) {
+    p.lay = h->ldpc_mode == DTL_LDPC_LAYERED && h->all_lay && !h->no_fast_bp;
+    p.lay_tab_bytes = h->lay_tab_bytes; p.lay_warp_bytes = h->lay_warp_bytes;
+    if (p.fast || p.lay) {
         p.cw_stride = (h->max_n + 3) & ~3;           // 16-byte multiples: one bulk copy per codeword
         p.cwbuf = sg.scratch<float>(SL_CWBUF, (size_t)p.cw_cap * p.cw_stride);
         p.items = sg.scratch<BpItem>(SL_BPITEMS, (size_t)p.cw_cap);
@@ -1121,6 +1173,8 @@ extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const fl
     p.fast = h->ldpc_mode == DTL_LDPC_REFERENCE && c.dev.fast && !h->no_fast_bp;
     p.fast_tab_bytes = (int)fast_tab_bytes(c.n, c.m, c.dev.nvr); p.fast_warp_bytes = (int)fast_warp_bytes(c.n, c.m, c.dev.rs);
     p.exp_tab = h->d_exp_tab; p.sigma2_lr = sigma2_for_lr(h->sigma2);
+    p.lay = h->ldpc_mode == DTL_LDPC_LAYERED && c.dev.lay_steps > 0 && !h->no_fast_bp;
+    p.lay_tab_bytes = (int)lay_tab_bytes(c.n, c.m, c.dev.lay_steps); p.lay_warp_bytes = (int)lay_warp_bytes(c.n, c.m, c.dev.rs);
     p.llr = sg.in(SL_LLR, llr, (size_t)count * c.n);
     p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
     p.nit = sg.out(SL_NIT, nit, (size_t)count);

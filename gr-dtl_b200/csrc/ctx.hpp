@@ -89,6 +89,8 @@ struct CodeDev {
     int uniform_rows;            // every row has exactly max_row edges
     int nvr;                     // variable rounds: ceil(n / 32)
     const uint4* rv2;            // [m] variables of the row's edges as 8 x u16 in mlist order (pad: n)
+    int lay_steps;               // layered decoder (bp_layered.cuh): groups of variable-disjoint rows, one step each
+    const uint16_t* lay_rows;    // [lay_steps][32][8] per (step, lane): the row's variables (pad: n), [7] = row id (0xffff = idle)
     const uint4* vdesc;          // [nvr*32] one entry per (round, lane): x = slot0 | slot1 << 16, y = slot2 | slot3 << 16 in nlist
                                  //   order (pad: the dummy slot m*rs, which holds 1.0), z = variable (idle lane: n + 1)
 };
@@ -128,6 +130,7 @@ struct Code {                    // host copy
     std::vector<int> permute;
     std::vector<std::vector<uint8_t>> P;   // rank x k parity part (for the TX-side encoder)
     CodeDev dev{};
+    int lay_shared = 0;          // variable occurrences beyond the first inside one step of the layered schedule (api.cc: schedule_rows)
     int bank_extra = 0;          // shared-memory wavefronts beyond one per access the variable order leaves (api.cc: order_variables)
     std::string path;
 };

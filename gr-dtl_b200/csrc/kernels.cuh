@@ -25,6 +25,15 @@ __host__ __device__ inline size_t fast_warp_bytes(int n, int m, int rs)
 {
     return ((size_t)m * rs + 2) * 8 + ((((size_t)n + 2) * 8 + 15) & ~(size_t)15) + (((size_t)n + 2 + 15) & ~(size_t)15);   // msg, lr0, est: 16-byte multiples (rs is even)
 }
+// layered decoder (bp_layered.cuh)
+__host__ __device__ inline size_t lay_tab_bytes(int n, int m, int steps)
+{
+    return 16 * (size_t)m + 512 * (size_t)steps + ((2 * (size_t)n + 15) & ~(size_t)15);
+}
+__host__ __device__ inline size_t lay_warp_bytes(int n, int m, int rs)
+{
+    return (((size_t)m * rs * 4 + 15) & ~(size_t)15) + ((((size_t)n + 2) * 4 + 15) & ~(size_t)15) + (((size_t)n + 2 + 15) & ~(size_t)15);
+}
 inline bool bp_ref_has_instance(int max_row, int max_col)
 {
     return max_row >= 3 && max_row <= 8 && max_col >= 1 && max_col <= 4 && !(max_row == 3 && max_col > 3);
@@ -108,6 +117,7 @@ struct FecParams {
     int max_it; double sigma2; int mode; int warp_bytes;
     // reference mode on codes bp_ref.cuh has an instance for (all codes of the handle): ldpc_bp_ref_kernel
     int fast; int fast_tab_bytes, fast_warp_bytes; const double2* exp_tab;
+    int lay; int lay_tab_bytes, lay_warp_bytes;    // layered mode on codes with row-major tables: ldpc_bp_lay_kernel
     double sigma2_lr;                              // sigma2, or -(1/sigma2) when sigma2 is a power of two (lr_of_rx)
     float* cwbuf; int cw_stride;                   // [queued codewords][cw_stride] received values in H column order (bp_gather_kernel)
     BpItem* items;                                 // [queued codewords]
@@ -120,6 +130,7 @@ struct LdpcParams {                                // stand-alone fec_dec::decod
     CodeDev code; const float* llr; long long count; uint8_t* bits; int* nit; int max_it; double sigma2; int mode;
     int* cursor; int warp_bytes; int tab_bytes;
     int fast; int fast_tab_bytes, fast_warp_bytes; const double2* exp_tab; double sigma2_lr;
+    int lay; int lay_tab_bytes, lay_warp_bytes;
 };
 
 // ---- TX FEC framer --------------------------------------------------------------------------------

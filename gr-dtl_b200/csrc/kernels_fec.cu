@@ -25,6 +25,7 @@
 // counts match the reference; DTL_LDPC_LAYERED is a layered normalised min-sum in fp32 (throughput mode).
 #include "kernels.cuh"
 #include "bp_ref.cuh"
+#include "bp_layered.cuh"
 #include <cstdlib>
 
 namespace dtl {
@@ -877,7 +878,13 @@ __global__ void __launch_bounds__(256) bp_gather_kernel(FecParams p)
             if (lo < hi) {
                 const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
                                               : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
-                for (int g = lo + lane; g < hi; g += 32) dst[g - rcv_idx] = -1 * __ldcs(&src[g - base]);
+                for (int g0 = lo + lane; g0 < hi; g0 += 320) {           // ten loads per lane in flight: a whole n <= 320 codeword
+                    float xv[10];
+#pragma unroll
+                    for (int u = 0; u < 10; u++) { const int g = g0 + 32 * u; xv[u] = g < hi ? __ldcs(&src[g - base]) : 0.f; }
+#pragma unroll
+                    for (int u = 0; u < 10; u++) { const int g = g0 + 32 * u; if (g < hi) dst[g - rcv_idx] = -1 * xv[u]; }
+                }
             }
             base += sg.len;
         }
@@ -963,6 +970,92 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
         if (tid == 0) p.cw_nit[rec.it] = nit;
         team_sync<NT>(bar_id);
         j = nxt; rec = nrec;
+    }
+}
+
+// Pass 2, layered mode (bp_layered.cuh): the same queue, gathered blocks and bulk-copy prefetch as ldpc_bp_ref_kernel, one
+// codeword per warp; the block's received values ARE the initial posteriors (no likelihood-ratio pass).
+template <int W, int MINB>
+__global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ LayS scodes[DTL_MAX_SMEM_CODES];
+    __shared__ __align__(8) uint64_t bars[W];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    {
+        int off = 0;
+        for (int ci = 1; ci <= p.n_codes; ci++) {
+            const CodeDev g = p.codes[ci];
+            const LayS sc = stage_lay(g, sm, off);
+            if (threadIdx.x == 0) scodes[ci] = sc;
+            off += (int)lay_tab_bytes(g.n, g.m, g.lay_steps);
+        }
+        if (lane == 0) mbar_init(&bars[wid], 1);
+        __syncthreads();
+    }
+    const int stg_bytes = p.cw_stride * 4;
+    unsigned char* base = sm + p.lay_tab_bytes + (size_t)wid * (p.lay_warp_bytes + stg_bytes);
+    float* stg = (float*)(base + p.lay_warp_bytes);
+    uint64_t* bar = &bars[wid];
+    const int total = p.cnt[3] + p.cnt[5] + p.cnt[6] + p.cnt[7];
+    int j = 0;
+    if (lane == 0) j = atomicAdd(&p.cnt[1], 1);
+    j = __shfl_sync(0xffffffffu, j, 0);
+    BpItem rec;
+    rec.out_off = 0; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.pad = 0;
+    if (j < total) {
+        if (lane == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)j * p.cw_stride, (uint32_t)stg_bytes, bar); }
+        rec = p.items[j];
+    }
+    uint32_t phase = 0;
+    while (j < total) {
+        int nxt = 0;
+        if (lane == 0) nxt = atomicAdd(&p.cnt[1], 1);
+        LayS c = scodes[rec.fec_id];
+        c.smb = sm;
+        const LayBuf w = lay_carve(base, c.n, c.m, c.rs);
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        for (int q = lane; q < c.n; q += 32) w.post[c.permute()[q]] = stg[q];       // ldpc_dec.cc:64-66 (the block holds -llr)
+        __syncwarp();
+        nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        BpItem nrec = rec;
+        if (nxt < total) {
+            if (lane == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)nxt * p.cw_stride, (uint32_t)stg_bytes, bar); }
+            nrec = p.items[nxt];
+        }
+        const int nit = bp_lay_run(c, w, lane, p.max_it);
+        uint8_t* out = p.bits + rec.out_off;
+        for (int q = lane; q < rec.k_; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
+        if (lane == 0) p.cw_nit[rec.it] = nit;
+        __syncwarp();
+        j = nxt; rec = nrec;
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) ldpc_plain_lay_kernel(LdpcParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    LayS c = stage_lay(p.code, sm, 0);
+    c.smb = sm;
+    __syncthreads();
+    const LayBuf w = lay_carve(sm + p.lay_tab_bytes + (size_t)wid * p.lay_warp_bytes, c.n, c.m, c.rs);
+    for (;;) {
+        long long it = 0;
+        if (lane == 0) it = atomicAdd(p.cursor, 1);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= p.count) break;
+        const float* in = p.llr + it * c.n;
+        for (int q = lane; q < c.n; q += 32) w.post[c.permute()[q]] = -1 * in[q];
+        if (lane == 0) { w.post[c.n] = 1.0e30f; w.est[c.n] = 0; }
+        __syncwarp();
+        int nit = 0;
+        if (lay_syndrome<8>(c, w, lane)) nit = bp_lay_run(c, w, lane, p.max_it);
+        uint8_t* out = p.bits + it * c.k;
+        for (int q = lane; q < c.k; q += 32) out[q] = w.est[c.permute()[c.rank + q]];
+        if (lane == 0 && p.nit) p.nit[it] = nit;
+        __syncwarp();
     }
 }
 
@@ -1223,6 +1316,17 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         if (le != cudaSuccess) return le;
         if (launches) *launches += 1;
         prof->end();
+    } else if (p.lay) {   // pass 2, layered mode on codes with row-major tables (bp_layered.cuh)
+        bp_gather_kernel<<<sm_count * 8, 256, 0, st>>>(p);
+        const int W = 8;
+        const size_t sm_bytes = (size_t)p.lay_tab_bytes + ((size_t)p.lay_warp_bytes + (size_t)p.cw_stride * 4) * W;
+        if (sm_bytes + 256 > 227 * 1024) return cudaErrorInvalidConfiguration;
+        int per_sm = (int)((227 * 1024) / (sm_bytes + 1024 + 256));
+        if (per_sm < 1) per_sm = 1;
+        if (per_sm > 4) per_sm = 4;
+        ldpc_bp_lay_kernel<8, 4><<<sm_count * per_sm, W * 32, sm_bytes, st>>>(p);
+        if (launches) *launches += 1;
+        prof->end();
     } else {   // pass 2: belief propagation on what did not pass, persistent
         const int warps = DTL_BP_WARPS;
         const size_t smem = (size_t)p.tab_bytes + (size_t)p.warp_bytes * warps;
@@ -1259,6 +1363,8 @@ cudaError_t init_kernels_fec()
     if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_ref_kernel<32, 6, 3>);
     if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_ref_kernel<64, 4, 4>);
     if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_plain_ref_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_bp_lay_kernel<8, 4>);
+    if (e == cudaSuccess) e = set_max_dyn_smem(ldpc_plain_lay_kernel);
     return e;
 }
 
@@ -1278,6 +1384,12 @@ cudaError_t launch_ldpc(cudaStream_t st, const LdpcParams& p, int sm_count)
         const size_t fsmem = (size_t)p.fast_tab_bytes + (size_t)p.fast_warp_bytes * warps;
         if (fsmem > 227 * 1024) return cudaErrorInvalidConfiguration;
         ldpc_plain_ref_kernel<<<blocks, warps * 32, fsmem, st>>>(p);
+    } else if (p.lay) {
+        const size_t lsmem = (size_t)p.lay_tab_bytes + (size_t)p.lay_warp_bytes * 8;
+        if (lsmem > 227 * 1024) return cudaErrorInvalidConfiguration;
+        long long lb = (p.count + 7) / 8;
+        if (lb > (long long)sm_count * 4) lb = (long long)sm_count * 4;
+        ldpc_plain_lay_kernel<<<(unsigned)lb, 256, lsmem, st>>>(p);
     } else ldpc_plain_kernel<<<blocks, warps * 32, smem, st>>>(p);
     return cudaGetLastError();
 }
