@@ -510,8 +510,16 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
     std::vector<float2> tw(N);
     for (int j = 0; j < N; j++) { const double a = -2.0 * M_PI * j / N; tw[j] = make_float2((float)std::cos(a), (float)std::sin(a)); }
     h->tw = h->upload(tw, e);
-    std::vector<uint32_t> crc(256);
+    // [0]: the byte table; [1..4]: the CRC register after 16 zero bytes, per byte of the register (eq_fast_kernel MODE 2:
+    // crc32_warp strings 16-byte chunk CRCs together)
+    std::vector<uint32_t> crc(5 * 256);
     for (uint32_t i = 0; i < 256; i++) { uint32_t r = i; for (int k = 0; k < 8; k++) r = (r & 1) ? (r >> 1) ^ 0xEDB88320u : r >> 1; crc[i] = r; }
+    for (int j = 0; j < 4; j++)
+        for (uint32_t b = 0; b < 256; b++) {
+            uint32_t r = b << (8 * j);
+            for (int z = 0; z < 16; z++) r = crc[r & 0xffu] ^ (r >> 8);
+            crc[256 * (1 + j) + b] = r;
+        }
     h->crc_table = h->upload(crc, e);
 
     // ---- MCS look-up table (ofdm_adaptive_feedback_decision.cc:33-53: lut[0].first = DBL_MIN)

@@ -1238,17 +1238,25 @@ __global__ void __launch_bounds__(128) tb_gather_kernel(FecParams p)
     for (int i = wid; i < ntb; i += warps) {
         const int n = s_nb[i];
         if (n <= 0) continue;
-        const uint8_t* src = p.bits + s_bb[i];
+        const uint8_t* src = p.bits + s_bb[i];                 // 4-byte aligned (bit offsets are multiples of 4)
         uint8_t* dst = p.bytes + (size_t)s * p.bytes_cap + s_pos[i];
-        for (int b = lane; b < n; b += 32) dst[b] = src[b];
+        if ((((uintptr_t)dst) & 3) == 0) {
+            const int nw = n >> 2;
+            for (int w = lane; w < nw; w += 32) ((uint32_t*)dst)[w] = ((const uint32_t*)src)[w];
+            for (int b = (nw << 2) + lane; b < n; b += 32) dst[b] = src[b];
+        } else
+            for (int b = lane; b < n; b += 32) dst[b] = src[b];
     }
 }
 
-// One warp per stream: LLRs of the TB still in flight move behind what the carry buffer already holds.
+// LLRs of the TB still in flight move behind what the carry buffer already holds.  grid = (streams, chunks): block (s, c)
+// copies floats [c * CHUNK, (c + 1) * CHUNK) of the stream's pending run (a TB of the scaled PHY is 31 k LLRs: one warp per
+// stream took 0.48 ms on 256 streams).  The sign words of the carry buffer (screening pass of the next call) follow in
+// carry_sign_kernel, after every block of this one is done.
+#define DTL_CARRY_CHUNK 4096
 __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
 {
-    const int lane = threadIdx.x & 31;
-    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int s = blockIdx.x, c0 = blockIdx.y * DTL_CARRY_CHUNK;
     if (s >= p.n_streams) return;
     const TbDesc& d = p.pend[s];
     float* carry = p.carry + (size_t)s * p.carry_cap;
@@ -1257,18 +1265,26 @@ __global__ void __launch_bounds__(256) carry_save_kernel(FecParams p)
         const TbSeg sg = d.seg[i];
         if (sg.src >= 0) {
             const float* src = p.llr + ((size_t)s * p.F + sg.src) * p.llr_stride + sg.start;
-            for (int q = lane; q < sg.len; q += 32) carry[base + q] = src[q];
+            const int lo = max(base, c0), hi = min(base + sg.len, c0 + DTL_CARRY_CHUNK);
+            for (int q = lo + threadIdx.x; q < hi; q += blockDim.x) carry[q] = src[q - base];
         }                                      // src < 0: the carry segment is always first and already in place
         base += sg.len;
     }
-    if (p.csgn) {                              // the carry buffer's sign words for the next call's screening pass
-        __syncwarp();
-        uint32_t* cs = p.csgn + (size_t)s * p.csgn_stride;
-        for (int q0 = 0; q0 < base; q0 += 32) {
-            const bool bit = q0 + lane < base && carry[q0 + lane] > 0.f;
-            const unsigned word = __ballot_sync(0xffffffffu, bit);
-            if (lane == 0) cs[q0 >> 5] = word;
-        }
+}
+
+__global__ void __launch_bounds__(256) carry_sign_kernel(FecParams p)
+{
+    const int s = blockIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (s >= p.n_streams) return;
+    const TbDesc& d = p.pend[s];
+    int len = 0;
+    for (int i = 0; i < d.nseg; i++) len += d.seg[i].len;
+    const float* carry = p.carry + (size_t)s * p.carry_cap;
+    uint32_t* cs = p.csgn + (size_t)s * p.csgn_stride;
+    for (int q0 = (blockIdx.y * (blockDim.x >> 5) + wid) * 32; q0 < len; q0 += gridDim.y * blockDim.x) {
+        const bool bit = q0 + lane < len && carry[q0 + lane] > 0.f;
+        const unsigned word = __ballot_sync(0xffffffffu, bit);
+        if (lane == 0) cs[q0 >> 5] = word;
     }
 }
 
@@ -1276,6 +1292,13 @@ __global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used)
 {
     cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; cnt[5] = cnt[6] = cnt[7] = 0;     // cnt[4] is the stand-alone decoder's cursor
     *bits_used = 0ull;
+}
+
+static void launch_carry_save(cudaStream_t st, const FecParams& p)
+{
+    const int chunks = (p.carry_cap + DTL_CARRY_CHUNK - 1) / DTL_CARRY_CHUNK;
+    carry_save_kernel<<<dim3(p.n_streams, chunks), 256, 0, st>>>(p);
+    if (p.csgn) carry_sign_kernel<<<dim3(p.n_streams, (chunks + 1) / 2), 256, 0, st>>>(p);
 }
 
 cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* launches, Prof* prof, int phase,
@@ -1340,15 +1363,15 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     if (side && ev) {
         cudaEventRecord(ev, st);
         cudaStreamWaitEvent(side, ev, 0);
-        carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, side>>>(p);
+        launch_carry_save(side, p);
     }
     const int tb_max = p.n_streams * p.tb_slots;
     prof->begin(DTL_STAGE_TBFINISH, 3);
     tb_finish_kernel<<<(tb_max + 7) / 8, 256, 0, st>>>(p);
     tb_gather_kernel<<<p.n_streams, 128, 0, st>>>(p);
-    if (!(side && ev)) carry_save_kernel<<<(p.n_streams + 7) / 8, 256, 0, st>>>(p);
+    if (!(side && ev)) launch_carry_save(st, p);
     prof->end();
-    if (launches) *launches += 5;
+    if (launches) *launches += p.csgn ? 6 : 5;
     return cudaGetLastError();
 }
 
