@@ -39,7 +39,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_CWBUF, SL_BPITEMS, SL_SGN, SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
+    SL_CWBUF, SL_BPITEMS, SL_SGN, SL_SYX, SL_SYFLAGS, SL_SYSEGS, SL_SYNSEG, SL_SYRAW, SL_SYFIXED, SL_SYSTARTS, SL_SYSTARTS_OUT, SL_SYNFR, SL_SYFRAMES, SL_SYVALID, SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
     SL_TXDATA, SL_TXLEN, SL_TXCNST, SL_TXFEC, SL_TXTBS, SL_TXNTB, SL_TXKEEP, SL_TXSEGS, SL_TXCRC, SL_TXBITS, SL_TXCHUNKS, SL_TXMETA, SL_TXCONS, SL_TXSTARTED, SL_COUNT
 };
 
@@ -92,6 +92,9 @@ struct dtl_b200 {
     cudaStream_t side_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_plan = nullptr, ev_eq = nullptr, ev_side = nullptr, ev_hdr = nullptr;
     bool side_pending = false, hdr_pending = false;
+    // synchronisation front end (dtl_b200_rx_stream): per-stream state, double-buffered work buffers
+    DevBuf sync_st, sync_w[2]; int sync_streams = -1, sync_cur = 0, sync_wcap = 0, sync_keep = 0, sync_tmax = 0; float sync_threshold = 0.95f;
+    const int* hdr_valid = nullptr;   // set for one dev_header call: frame slots that hold a frame
     bool no_fast_bp = false;          // DTL_BP_OLD=1: the first (slot-major) reference-mode decoder, for A/B runs
     const float2* fuse_iq = nullptr;  // set by rx_device for one dev_equalize call: FFT fused into the equaliser kernel   // hdr_pending: the header branch of this call runs on the side stream
     int overlap = -1;
@@ -246,7 +249,8 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
-    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->csgn_buf.release(); h->txst_buf.release(); h->txcarry_buf.release();
+    h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->csgn_buf.release();
+    h->sync_st.release(); h->sync_w[0].release(); h->sync_w[1].release(); h->txst_buf.release(); h->txcarry_buf.release();
     h->prof.release();
     for (int i = 0; i < 2; i++) {
         if (h->ev_h2d[i]) cudaEventDestroy(h->ev_h2d[i]);
@@ -685,7 +689,7 @@ extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
     if (prop.major != 10) { fail(h, DTL_ERR_UNSUPPORTED, "libdtl_b200 is built for sm_100a only"); return bail(DTL_ERR_UNSUPPORTED); }
     h->sm_count = prop.multiProcessorCount;
     // per-device kernel attributes (opt-in dynamic shared memory), set for THIS handle's device
-    for (cudaError_t (*init)() : { init_kernels_fft, init_kernels_eq, init_kernels_fec, init_kernels_hdr })
+    for (cudaError_t (*init)() : { init_kernels_fft, init_kernels_eq, init_kernels_fec, init_kernels_hdr, init_kernels_sync })
         if ((e = init()) != cudaSuccess) { cuda_fail(h, e, "cudaFuncSetAttribute"); return bail(DTL_ERR_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { cuda_fail(h, e, "cudaStreamCreate"); return bail(DTL_ERR_CUDA); }
     h->prof.st = h->stream;
@@ -693,6 +697,7 @@ extern "C" dtl_status dtl_b200_create(const dtl_config* c, dtl_b200** out)
     h->max_bps = c->max_bps; h->fec_enabled = c->fec_enabled;
     h->ldpc_max_it = c->ldpc_max_iterations > 0 ? c->ldpc_max_iterations : 15;
     h->ldpc_mode = c->ldpc_mode; h->sigma2 = c->ldpc_sigma2 > 0 ? c->ldpc_sigma2 : 2.0;
+    h->sync_threshold = c->sync_threshold > 0.f ? c->sync_threshold : 0.95f;
     h->n_mcs = c->n_mcs; h->initial_mcs = c->initial_mcs; h->decision_th = c->decision_th; h->hysteresis = c->hysteresis;
     dtl_status s = build_tables(h, c);
     if (s != DTL_OK) return bail(s);
@@ -732,6 +737,7 @@ extern "C" dtl_status dtl_b200_reset(dtl_b200* h, int32_t n_streams)
     h->launches += n_streams > 0 ? 1 : 0;
     CK(cudaMemsetAsync(h->d_err, 0, sizeof(int), h->stream));
     h->n_streams = n_streams;
+    h->sync_streams = -1;                        // and the synchronisation front end
     h->tx_streams = -1;                          // the TX framer starts over as well (state re-created by its next call)
     return DTL_OK;
 }
@@ -1409,6 +1415,7 @@ dtl_status dev_header(dtl_b200* h, Stage& sg, const float2* d_iq, int S, int F, 
     memset(&p, 0, sizeof p);
     p.hd = h->hd; p.pl = h->pl; p.cn = h->cn; p.hfreq = hfreq; p.n_frames = n; p.n_streams = S; p.F = F;
     p.meta = d_meta; p.taps = d_taps; p.hres = d_hres; p.st = (StreamState*)h->st_buf.p + h->s_off;
+    p.valid = h->hdr_valid; h->hdr_valid = nullptr;
     CK(launch_header(h->stream, p));
     h->prof.end();
     h->launches += 3;
@@ -1435,6 +1442,34 @@ extern "C" dtl_status dtl_b200_rx_headers(dtl_b200* h, const float* iq, int32_t 
     return sg.finish();
 }
 
+namespace {
+// header branch, then the payload branch on the tags it produced (device pointers).  valid: frame slots that hold a frame (or null)
+dtl_status rx_iq_device(dtl_b200* h, Stage& sg, const float2* d_iq, int S, int F, dtl_frame_meta* d_meta, float2* d_taps,
+                        dtl_header_result* d_hres, dtl_frame_result* d_res, uint8_t* d_bytes, int bytes_cap, int* d_nb,
+                        dtl_tb_result* d_tbs, int tb_cap, int* d_nt, int* d_fcrc, const int* valid)
+{
+    dtl_status s;
+    h->hdr_valid = valid;
+    if (side_on(h)) {
+        // the header branch (instruction-bound) runs on the side stream beside the payload FFT (HBM-bound), which needs neither
+        // tags nor taps; TB planning follows it on the same stream, the equaliser waits for it
+        CK(cudaEventRecord(h->ev_fork, h->stream));
+        CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+        std::swap(h->stream, h->side_stream);
+        s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres);
+        std::swap(h->stream, h->side_stream);
+        if (s != DTL_OK) return s;
+        CK(cudaEventRecord(h->ev_hdr, h->side_stream));
+        CK(cudaEventRecord(h->ev_side, h->side_stream));
+        h->hdr_pending = true; h->side_pending = true;
+    } else if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
+    s = rx_device(h, sg, 0, d_iq, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
+    if (s != DTL_OK) return s;
+    return DTL_OK;
+}
+} // namespace
+
+
 extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_streams, int32_t frames_per_stream,
                                      dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
                                      uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
@@ -1459,20 +1494,7 @@ extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_str
     int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
     int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
-    if (side_on(h)) {
-        // the header branch (instruction-bound) runs on the side stream beside the payload FFT (HBM-bound), which needs neither
-        // tags nor taps; TB planning follows it on the same stream, the equaliser waits for it
-        CK(cudaEventRecord(h->ev_fork, h->stream));
-        CK(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
-        std::swap(h->stream, h->side_stream);
-        s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres);
-        std::swap(h->stream, h->side_stream);
-        if (s != DTL_OK) return s;
-        CK(cudaEventRecord(h->ev_hdr, h->side_stream));
-        CK(cudaEventRecord(h->ev_side, h->side_stream));
-        h->hdr_pending = true; h->side_pending = true;
-    } else if ((s = dev_header(h, sg, d_iq, S, F, d_meta, d_taps, d_hres)) != DTL_OK) return s;
-    s = rx_device(h, sg, 0, d_iq, d_taps, d_meta, S, F, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc);
+    s = rx_iq_device(h, sg, d_iq, S, F, d_meta, d_taps, d_hres, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc, nullptr);
     if (s != DTL_OK) return s;
     return sg.finish();
 }
@@ -1547,5 +1569,76 @@ extern "C" dtl_status dtl_b200_tx(dtl_b200* h, const uint8_t* hdr_bits, const ui
     CK(launch_tx_mod(h->stream, p));
     h->prof.end();
     h->launches += 1;
+    return sg.finish();
+}
+
+// ---- synchronisation front end + receive path ---------------------------------------------
+extern "C" dtl_status dtl_b200_rx_stream(dtl_b200* h, const float* iq, int32_t n_streams, int64_t samples_per_stream, int32_t frames_cap,
+                                         int32_t* n_frames, int64_t* frame_start, float* frames_out,
+                                         dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
+                                         uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                                         dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem)
+{
+    if (!h || !iq || !n_frames || n_streams <= 0 || samples_per_stream <= 0 || frames_cap <= 0) return DTL_ERR_INVALID_ARG;
+    if (samples_per_stream > 0x3fffffff) return DTL_ERR_INVALID_ARG;
+    if ((bytes && bytes_cap <= 0) || (tbs && tb_cap <= 0)) return DTL_ERR_INVALID_ARG;
+    if (!h->have_hdr) return fail(h, DTL_ERR_INVALID_ARG, "dtl_b200_rx_stream needs the sync words");
+    CK(cudaSetDevice(h->device));
+    const int S = n_streams, F = frames_cap, T = (int)samples_per_stream, FS = h->frame_samples, N = h->N;
+    const size_t n = (size_t)S * F;
+    dtl_status s = ensure_streams(h, S);
+    if (s != DTL_OK) return s;
+    if (h->sync_streams != S) {                  // first call (or after dtl_b200_reset): detector / regulariser state starts empty
+        CK(cudaStreamSynchronize(h->stream));
+        h->sync_keep = FS + 2 * (N + h->cp) + 2 * N + 64;
+        h->sync_tmax = T;
+        h->sync_wcap = h->sync_keep + T;
+        CK(h->sync_st.ensure(std::max<size_t>((size_t)S * sizeof(SyncState), 16)));
+        for (int b = 0; b < 2; b++) CK(h->sync_w[b].ensure((size_t)S * h->sync_wcap * sizeof(float2) + 16));
+        CK(launch_sync_reset(h->stream, (SyncState*)h->sync_st.p, S));
+        h->sync_cur = 0;
+        h->sync_streams = S;
+    }
+    if (T > h->sync_tmax) return fail(h, DTL_ERR_CAPACITY, "samples_per_stream larger than in the first call after dtl_b200_reset");
+    Stage sg(h, mem);
+    SyncParams p;
+    memset(&p, 0, sizeof p);
+    p.st = (SyncState*)h->sync_st.p; p.n_streams = S; p.T = T; p.N = N; p.cp = h->cp; p.FS = FS; p.threshold = h->sync_threshold;
+    p.x = sg.in(SL_SYX, (const float2*)iq, (size_t)S * T);
+    p.w_old = (const float2*)h->sync_w[h->sync_cur].p; p.w_new = (float2*)h->sync_w[h->sync_cur ^ 1].p;
+    p.w_cap = h->sync_wcap; p.keep_cap = h->sync_keep;
+    p.flag_words = (T + h->sync_keep) / 32 + 64;
+    p.flags = sg.scratch<uint32_t>(SL_SYFLAGS, (size_t)S * p.flag_words);
+    p.seg_cap = 2 * F + 16 + DTL_SYNC_SEGC; p.trig_cap = 2 * F + 16;
+    p.segs = sg.scratch<SyncSeg>(SL_SYSEGS, (size_t)S * p.seg_cap);
+    p.n_seg = sg.scratch<int>(SL_SYNSEG, (size_t)S * 3); p.n_raw = p.n_seg + S; p.n_fixed = p.n_seg + 2 * S;
+    p.raw = sg.scratch<long long>(SL_SYRAW, (size_t)S * p.trig_cap);
+    p.fixed = sg.scratch<long long>(SL_SYFIXED, (size_t)S * p.trig_cap);
+    p.frames_cap = F;
+    p.starts = sg.scratch<long long>(SL_SYSTARTS, n);
+    p.starts_out = frame_start ? (long long*)sg.out(SL_SYSTARTS_OUT, (long long*)frame_start, n) : nullptr;
+    p.n_frames = sg.out(SL_SYNFR, n_frames, (size_t)S);
+    float2* d_frames = frames_out ? sg.out(SL_SYFRAMES, (float2*)frames_out, n * FS) : sg.scratch<float2>(SL_SYFRAMES, n * FS);
+    p.frames = d_frames;
+    p.valid = sg.scratch<int>(SL_SYVALID, n);
+    p.err = h->d_err;
+    dtl_frame_meta* d_meta = meta_out ? sg.out(SL_HMETA, meta_out, n) : sg.scratch<dtl_frame_meta>(SL_HMETA, n);
+    float2* d_taps = sg.scratch<float2>(SL_HTAPS, n * N);
+    dtl_header_result* d_hres = hres ? sg.out(SL_HRES, hres, n) : nullptr;
+    dtl_frame_result* d_res = sg.out(SL_RES, res, n);
+    uint8_t* d_bytes = sg.out(SL_BYTES, bytes, (size_t)S * bytes_cap);
+    int* d_nb = sg.out(SL_NBYTES, nbytes, (size_t)S);
+    dtl_tb_result* d_tbs = sg.out(SL_TBS_OUT, tbs, (size_t)S * tb_cap);
+    int* d_nt = sg.out(SL_NTBS, ntbs, (size_t)S);
+    int* d_fcrc = sg.out(SL_FCRC, frame_crc, n);
+    if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
+    int launches = 0;
+    h->prof.begin(DTL_STAGE_SYNC, 4);
+    CK(launch_sync(h->stream, p, &launches));
+    h->prof.end();
+    h->launches += launches;
+    h->sync_cur ^= 1;
+    s = rx_iq_device(h, sg, d_frames, S, F, d_meta, d_taps, d_hres, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc, p.valid);
+    if (s != DTL_OK) return s;
     return sg.finish();
 }

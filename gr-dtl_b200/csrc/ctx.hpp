@@ -110,6 +110,19 @@ struct StreamState {
     int hdr_cnst;                // header parser's fallback constellation (ofdm_adaptive_packet_header.cc:70,287-289)
 };
 
+// Synchronisation front end (kernels_sync.cu): per-stream state that survives between calls
+#define DTL_SYNC_PEND 4
+#define DTL_SYNC_SEGC 6
+struct SyncSeg { long long t; double ph; float f; int pad; };   // oscillator: phase[t] = ph, slope -2/N * f per sample from t on
+struct SyncState {
+    long long total, scan_pos, scan_lo, chunk_pos, busy_until, base_next, base_cur;
+    int keep_off, keep_len, len_cur, npend, nsegc;
+    long long pend[DTL_SYNC_PEND];
+    SyncSeg segc[DTL_SYNC_SEGC];
+    // ofdm_adaptive_frame_detect_bb_impl members (lib/dtl/ofdm_adaptive_frame_detect_bb_impl.h)
+    int d_remainder, d_missing_count, d_correction_count, d_acc_error, d_trigger_counter, d_synced, d_in_sync, d_error_count;
+};
+
 // TX FEC framer (kernels_txf.cu): per-stream state that survives between calls, and the per-call plan
 struct TxStream { int tb_count, frame_count; int rem, total; int cur_fec, cur_payload; };   // rem/total: bits of the TB in flight
 struct TxTb { int fec_id, ncws, payload_bytes, in_off, bits; };

@@ -150,6 +150,23 @@ struct TxfParams {
 cudaError_t launch_txf(cudaStream_t st, const TxfParams& p, int* launches);
 cudaError_t launch_txf_reset(cudaStream_t st, TxStream* s, int n);
 
+// ---- synchronisation front end ----------------------------------------------------------------------
+struct SyncParams {
+    SyncState* st; int n_streams; int T, N, cp, FS; float threshold;
+    const float2* x;                               // [S][T] the call's new samples
+    const float2* w_old; float2* w_new; int w_cap, keep_cap;     // per-stream work buffers [S][w_cap], double-buffered
+    uint32_t* flags; int flag_words;               // [S][flag_words] metric >= threshold, one bit per position
+    SyncSeg* segs; int seg_cap; int* n_seg;        // [S][seg_cap] phase segments of this call (carried ones first)
+    long long* raw; long long* fixed; int trig_cap; int* n_raw; int* n_fixed;   // [S][trig_cap] raw / regularised triggers
+    long long* starts; long long* starts_out; int frames_cap; int* n_frames;    // [S][frames_cap] frame starts (delayed coordinates)
+    float2* frames; int* valid;                    // [S][frames_cap][FS], [S][frames_cap]
+    int* err;
+};
+cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches);
+cudaError_t launch_sync_reset(cudaStream_t st, SyncState* state, int n);
+cudaError_t init_kernels_sync();
+size_t sync_metric_smem(int N);
+
 // ---- header branch ----------------------------------------------------------------------------------------------
 struct HdrParams {
     HdrDev hd; PlanDev pl; CnstDev cn;
@@ -157,6 +174,7 @@ struct HdrParams {
     long long n_frames; int n_streams, F;
     dtl_frame_meta* meta; float2* taps; dtl_header_result* hres;
     StreamState* st;
+    const int* valid;                              // [n_frames] or null: 0 = an empty frame slot (dtl_b200_rx_stream), dropped like a CRC failure
 };
 
 struct DemapParams {

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(256) header_kernel(HdrParams p, int G, int gro
         unsigned v = 0;
         if (lane <= nf) v = hdr_field(bits, nbits, start, fw, &got);
         const unsigned want = got >= 16 ? calc : (calc & ((1u << got) - 1u));       // compared while k < header_len only
-        const int ok = __shfl_sync(0xffffffffu, (int)(v == want), nf);
+        const int ok = __shfl_sync(0xffffffffu, (int)(v == want), nf) && (!p.valid || p.valid[f]);
         // dtl_frame_meta word j <- field: constellation 2, carrier_offset -, frame_no 1, payload_len 0, packet_len -,
         // fec_id 7, tb_no 4, tb_offset 6, tb_payload 8, reserved -   (raw constellation: header_fix_kernel applies the fallback)
         const int srcmap = lane == 0 ? 2 : lane == 2 ? 1 : lane == 3 ? 0 : lane == 5 ? 7 : lane == 6 ? 4 : lane == 7 ? 6 : lane == 8 ? 8 : 31;

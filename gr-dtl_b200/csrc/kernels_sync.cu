@@ -1,0 +1,352 @@
+// kernels_sync.cu -- synchronisation front end: S continuous IQ streams -> frames cut at their
+// boundaries, fine carrier-frequency offset removed.  Replaces, per stream (python/dtl/ofdm_receiver.py:70-97):
+//   digital.ofdm_sync_sc_cfb(fft_len, cp_len, threshold)   Schmidl & Cox timing metric, plateau detector, fine-CFO estimate
+//   blocks.delay(fft_len + cp_len) + analog.frequency_modulator_fc(-2 / fft_len) + blocks.multiply_cc
+//   dtl.ofdm_adaptive_frame_detect_bb(frame samples)       lib/dtl/ofdm_adaptive_frame_detect_bb_impl.cc:64-156 (trigger regulariser)
+//   digital.header_payload_demux (its trigger input)       frames start at the regularised triggers
+//
+// Three kernels per call over the stream's work buffer W = [samples kept from earlier calls | the call's new samples]:
+//   sync_metric_kernel  per tile of 1024 positions: c[m] = -x[m] conj(x[m - N/2]) and e[m] = 0.5 |x[m]|^2 into shared memory,
+//                       window sums over N/2 (complex) and N (real) samples as suffix-of-previous-block + prefix-of-current-block
+//                       (blocks aligned to the global sample index, fixed summation order: the same floats whatever the caller's
+//                       chunking), metric |P|^2 / E^2 >= threshold as one bit per position;
+//   sync_scan_kernel    one thread per stream, sequential but sparse: plateau detector on the bit words, fine-CFO phase segments
+//                       (arg P at the raw triggers), the regulariser's byte loop walked event by event, the demux's busy rule;
+//   sync_cut_kernel     every completed frame: delayed samples times exp(j phase), phase piecewise linear between raw triggers.
+// The tail each stream still needs (metric history, delay line of frames not complete yet) is copied to the other work
+// buffer together with the next call's samples (sync_append_kernel).
+#include "kernels.cuh"
+
+namespace dtl {
+
+__device__ __forceinline__ float2 ld_w(const float2* w, long long n, long long base, int len)
+{
+    const long long i = n - base;
+    return (i >= 0 && i < len) ? w[i] : make_float2(0.f, 0.f);            // before the stream began: zeros (the delay lines' initial state)
+}
+
+// new work buffer = [kept tail of the old one | new samples]; also moves the per-stream bookkeeping on
+__global__ void __launch_bounds__(256) sync_append_kernel(SyncParams p)
+{
+    const int s = blockIdx.y;
+    const SyncState st = p.st[s];
+    const float2* src = p.w_old + (size_t)s * p.w_cap + st.keep_off;
+    float2* dst = p.w_new + (size_t)s * p.w_cap;
+    const float2* x = p.x + (size_t)s * p.T;
+    const int keep = st.keep_len, total = keep + p.T;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+        dst[i] = i < keep ? src[i] : __ldcs(&x[i - keep]);
+}
+
+// ---- Schmidl & Cox metric, one bit per position ------------------------------------------------------------------------
+// Tile of TILE positions starting at a multiple of TILE (global index).  Shared memory: x[TILE + N + N/2], c / prefix / suffix
+// of c [TILE + N] (float2), e / prefix / suffix of e [TILE + N] (float).
+template <int TILE>
+__global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int N = p.N, W1 = N / 2, W2 = N, s = blockIdx.y;
+    const SyncState st = p.st[s];
+    const int len = st.keep_len + p.T;
+    const long long base = st.base_next;                        // global index of W[0] for this call
+    const long long lo = st.scan_lo & ~(long long)(TILE - 1);   // first tile that holds a position to examine
+    const long long p0 = lo + (long long)blockIdx.x * TILE;
+    const long long total = st.total + p.T;
+    if (p0 >= total) return;
+    const float2* w = p.w_new + (size_t)s * p.w_cap;
+    float2* xs = (float2*)sm;                                   // x[p0 - N - W1 .. p0 + TILE)
+    float2* cs = xs + (TILE + N + W1);                          // c[p0 - N .. p0 + TILE)
+    float2* pc = cs + (TILE + N);
+    float2* sc = pc + (TILE + N);
+    float* es = (float*)(sc + (TILE + N));
+    float* pe = es + (TILE + N);
+    float* se = pe + (TILE + N);
+    const int nx = TILE + N + W1, nc = TILE + N;
+    for (int i = threadIdx.x; i < nx; i += blockDim.x) xs[i] = ld_w(w, p0 - N - W1 + i, base, len);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+        const float2 a = xs[i + W1], b = xs[i];                 // x[m], x[m - N/2], m = p0 - N + i
+        cs[i] = make_float2(-__fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)), -__fmaf_rn(a.y, b.x, -__fmul_rn(a.x, b.y)));
+        es[i] = __fmul_rn(0.5f, __fmaf_rn(a.x, a.x, __fmul_rn(a.y, a.y)));
+    }
+    __syncthreads();
+    // prefix (ascending) and suffix (descending) sums inside every aligned block: one thread per block
+    const int nb1 = nc / W1, nb2 = nc / W2;
+    for (int b = threadIdx.x; b < nb1 + nb2; b += blockDim.x) {
+        if (b < nb1) {
+            const int o = b * W1;
+            float2 acc = cs[o];
+            pc[o] = acc;
+            for (int i = 1; i < W1; i++) { acc.x = __fadd_rn(acc.x, cs[o + i].x); acc.y = __fadd_rn(acc.y, cs[o + i].y); pc[o + i] = acc; }
+            acc = cs[o + W1 - 1];
+            sc[o + W1 - 1] = acc;
+            for (int i = W1 - 2; i >= 0; i--) { acc.x = __fadd_rn(acc.x, cs[o + i].x); acc.y = __fadd_rn(acc.y, cs[o + i].y); sc[o + i] = acc; }
+        } else {
+            const int o = (b - nb1) * W2;
+            float acc = es[o];
+            pe[o] = acc;
+            for (int i = 1; i < W2; i++) { acc = __fadd_rn(acc, es[o + i]); pe[o + i] = acc; }
+            acc = es[o + W2 - 1];
+            se[o + W2 - 1] = acc;
+            for (int i = W2 - 2; i >= 0; i--) { acc = __fadd_rn(acc, es[o + i]); se[o + i] = acc; }
+        }
+    }
+    __syncthreads();
+    // window sums and the comparison: position n = p0 + j, index N + j in the c / e arrays
+    uint32_t* flags = p.flags + (size_t)s * p.flag_words;
+    for (int j = threadIdx.x; j < TILE; j += blockDim.x) {
+        const int i = N + j;
+        float2 P = pc[i];
+        if ((i + 1) % W1) { const float2 t = sc[i - W1 + 1]; P.x = __fadd_rn(P.x, t.x); P.y = __fadd_rn(P.y, t.y); }
+        float E = pe[i];
+        if ((i + 1) % W2) E = __fadd_rn(E, se[i - W2 + 1]);
+        const float m = __fdiv_rn(__fmaf_rn(P.x, P.x, __fmul_rn(P.y, P.y)), __fmul_rn(E, E));
+        const long long n = p0 + j;
+        const unsigned word = __ballot_sync(0xffffffffu, n < total && m >= p.threshold);
+        if ((threadIdx.x & 31) == 0) flags[(n - lo) >> 5] = word;
+    }
+}
+
+// P[n] with the summation order of sync_metric_kernel (the fine-CFO estimate is arg P at a raw trigger)
+__device__ float2 sync_p_at(const float2* w, long long n, long long base, int len, int N)
+{
+    const int W1 = N / 2;
+    auto c_at = [&](long long m) {
+        const float2 a = ld_w(w, m, base, len), b = ld_w(w, m - W1, base, len);
+        return make_float2(-__fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)), -__fmaf_rn(a.y, b.x, -__fmul_rn(a.x, b.y)));
+    };
+    const long long b0 = n - (n % W1);
+    float2 pre = c_at(b0);
+    for (long long m = b0 + 1; m <= n; m++) { const float2 c = c_at(m); pre.x = __fadd_rn(pre.x, c.x); pre.y = __fadd_rn(pre.y, c.y); }
+    if (n == b0 + W1 - 1) return pre;
+    float2 suf = c_at(b0 - 1);
+    for (long long m = b0 - 2; m >= n - W1 + 1; m--) { const float2 c = c_at(m); suf.x = __fadd_rn(suf.x, c.x); suf.y = __fadd_rn(suf.y, c.y); }
+    return make_float2(__fadd_rn(pre.x, suf.x), __fadd_rn(pre.y, suf.y));
+}
+
+__device__ __forceinline__ double sync_phase(const SyncSeg* segs, int nseg, long long n, int N)
+{
+    int k = -1;
+    for (int i = 0; i < nseg; i++) { if (segs[i].t <= n) k = i; else break; }
+    if (k < 0) return 0.0;
+    return segs[k].ph + (double)(n - segs[k].t) * (-2.0 / N) * (double)segs[k].f;
+}
+
+// One thread per stream: everything that is sequential in the stream, on the sparse events only.
+__global__ void __launch_bounds__(64) sync_scan_kernel(SyncParams p)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= p.n_streams) return;
+    SyncState st = p.st[s];
+    const int N = p.N, cp = p.cp, FS = p.FS, D = N + cp;
+    const int len = st.keep_len + p.T;
+    const long long base = st.base_next;
+    const float2* w = p.w_new + (size_t)s * p.w_cap;
+    const uint32_t* flags = p.flags + (size_t)s * p.flag_words;
+    const long long flo = st.scan_lo & ~1023ll;
+    st.total += p.T;
+    const long long total = st.total, c0 = st.chunk_pos, scan_end = total - cp;
+    auto flag = [&](long long n) -> bool { return n < total && ((flags[(n - flo) >> 5] >> ((n - flo) & 31)) & 1u); };
+    SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;              // [0] = the segment carried in, then this call's raw triggers
+    int nseg = 0;
+    for (int a = 0; a < st.nsegc; a++) segs[nseg++] = st.segc[a];
+    long long* raw = p.raw + (size_t)s * p.trig_cap;
+    int nraw = 0, err = 0;
+    // ---- plateau_detector_fb(max_len = cp, threshold): skip the zero words, then walk the run
+    long long i = st.scan_pos > c0 ? st.scan_pos : c0;
+    while (i < scan_end) {
+        const long long wi = (i - flo) >> 5;
+        const uint32_t word = flags[wi] >> ((i - flo) & 31);
+        if (!word) { i = flo + ((wi + 1) << 5); if (i > scan_end) i = scan_end; continue; }   // never past what the reference's i++ reaches
+        i += __ffs(word) - 1;
+        if (i >= scan_end) break;
+        int k = 1;
+        for (; k < cp; k++) if (!flag(i + k)) break;
+        if (k > 1) {
+            const long long t = i + k / 2;
+            if (nraw < p.trig_cap) raw[nraw++] = t; else err = 1;
+            const float2 P = sync_p_at(w, t, base, len, N);
+            const float f = (float)atan2((double)P.y, (double)P.x);
+            double ph = sync_phase(segs, nseg, t - 1, N) + (-2.0 / N) * (double)f;
+            ph = fmod(ph + 3.14159265358979323846, 6.28318530717958647692);
+            if (ph < 0) ph += 6.28318530717958647692;
+            if (nseg < p.seg_cap) { segs[nseg].t = t; segs[nseg].ph = ph - 3.14159265358979323846; segs[nseg].f = f; nseg++; } else err = 1;
+        }
+        i += k + cp;
+    }
+    st.scan_pos = i;
+    long long c1 = i > scan_end ? i : scan_end;
+    if (c1 < c0) c1 = c0;
+    // ---- ofdm_adaptive_frame_detect_bb_impl::fix_sync (:64-156) on the chunk [c0, c1): the byte loop, event by event.
+    // `out` of the reference is the raw trigger list plus the triggers the loop itself sets / clears ahead of its position.
+    long long* fixed = p.fixed + (size_t)s * p.trig_cap;
+    int nfixed = 0;
+    {
+        const int clen = (int)(c1 - c0);
+        int last = -st.d_remainder, idx0 = st.d_remainder;      // index = idx0 + i while no event resets it
+        bool found = false;
+        int r = 0;                                              // next raw trigger
+        int ipos = 0;                                           // loop position
+        while (ipos < clen) {
+            // next position where something happens: a raw trigger, or the missing-trigger rule on a zero
+            while (r < nraw && (int)(raw[r] - c0) < ipos) r++;     // (cannot happen: triggers behind the loop position were consumed)
+            const int tpos = r < nraw ? (int)(raw[r] - c0) : 0x7fffffff;
+            int mpos = 0x7fffffff;
+            if (st.d_in_sync) {
+                // index > FS + 10  <=>  i > FS + 10 - idx0;  or index > FS + 1 at i == clen - 1
+                long long a = (long long)FS + 11 - idx0;
+                if (a < ipos) a = ipos;
+                if (a < clen) mpos = (int)a;
+                else if ((long long)(clen - 1) + idx0 > FS + 1 && clen - 1 >= ipos) mpos = clen - 1;
+            }
+            if (tpos >= clen && mpos >= clen) break;
+            if (tpos <= mpos) {
+                const int ii = tpos;
+                r++;
+                const int diff = ii - last - FS;
+                if (st.d_acc_error) ++st.d_trigger_counter;
+                const int inst = diff < 0 ? -diff : diff;
+                if (inst == 1) st.d_acc_error += diff;
+                st.d_error_count += inst != 0;
+                if (inst <= 1) { if (st.d_synced < 3) ++st.d_synced; else st.d_in_sync = 1; } else { st.d_synced = 0; st.d_in_sync = 0; }
+                int keep_at = ii;
+                if (st.d_acc_error > 1 || (inst > 1 && inst < 10)) {
+                    if (last + FS < clen && last + FS >= 0) {    // >= 0: the reference writes before its buffer here
+                        last += FS;                              // out[i] = 0; out[last] = 1; i = last
+                        keep_at = last;
+                        st.d_acc_error = 0;
+                        ++st.d_correction_count;
+                        // a jump forward passes over raw triggers: they stay in the output as they came in, unvisited
+                        while (r < nraw && (int)(raw[r] - c0) < keep_at) { if (nfixed < p.trig_cap) fixed[nfixed++] = raw[r]; else err = 1; r++; }
+                        if (r < nraw && (int)(raw[r] - c0) == keep_at) r++;
+                    } else last = ii;
+                } else last = ii;
+                if (nfixed < p.trig_cap) fixed[nfixed++] = c0 + keep_at; else err = 1;
+                ipos = keep_at + 1;                              // ++i after `i = last` (or after the trigger itself)
+                idx0 = -keep_at;                                 // index = 0 at the trigger: index = i - keep_at from here on
+                st.d_remainder = clen - last;
+                found = true;
+                if (st.d_trigger_counter > 10) st.d_acc_error = 0;
+            } else {
+                const int ii = mpos;
+                last += FS;
+                if (last < 0) last = ii;                         // same guard
+                if (nfixed < p.trig_cap) fixed[nfixed++] = c0 + last; else err = 1;
+                ipos = last + 1;
+                idx0 = -last;
+                found = true;
+                st.d_remainder = clen - last;
+                ++st.d_missing_count;
+                if (--st.d_synced < 3 - 5) { st.d_in_sync = 0; st.d_synced = 0; }
+            }
+        }
+        if (!found) st.d_remainder += clen;
+    }
+    st.chunk_pos = c1;
+    // `fixed` is in visiting order; triggers moved backwards can break the ascending order: sort (insertion, a handful of entries)
+    for (int a = 1; a < nfixed; a++) { const long long v = fixed[a]; int b = a - 1; while (b >= 0 && fixed[b] > v) { fixed[b + 1] = fixed[b]; b--; } fixed[b + 1] = v; }
+    // ---- header_payload_demux: a trigger starts a frame unless one is being copied; frames complete when their last sample is in
+    long long* starts = p.starts + (size_t)s * p.frames_cap;
+    int nfr = 0, npend = 0;
+    long long pend[DTL_SYNC_PEND];
+    long long cand[DTL_SYNC_PEND];
+    for (int a = 0; a < st.npend; a++) cand[a] = st.pend[a];
+    int ncand = st.npend;
+    auto place = [&](long long t) {
+        if (t - D + FS <= total) { if (nfr < p.frames_cap) starts[nfr++] = t; else err = 2; }
+        else if (npend < DTL_SYNC_PEND) pend[npend++] = t; else err = 1;
+    };
+    for (int a = 0; a < ncand; a++) place(cand[a]);
+    for (int a = 0; a < nfixed; a++) { const long long t = fixed[a]; if (t >= st.busy_until) { st.busy_until = t + FS; place(t); } }
+    st.npend = npend;
+    for (int a = 0; a < npend; a++) st.pend[a] = pend[a];
+    p.n_frames[s] = nfr;
+    p.n_seg[s] = nseg;
+    if (p.n_raw) p.n_raw[s] = nraw;
+    if (p.n_fixed) p.n_fixed[s] = nfixed;
+    // ---- what the next call still needs from the work buffer
+    long long keep = st.scan_pos - (N + N / 2);
+    if (c1 - D < keep) keep = c1 - D;
+    if (npend && pend[0] - D < keep) keep = pend[0] - D;
+    if (keep < base) keep = base;
+    if (keep > base + len) keep = base + len;
+    st.keep_off = (int)(keep - base);
+    st.keep_len = (int)(base + len - keep);
+    st.base_next = keep;
+    st.scan_lo = st.scan_pos > c1 ? st.scan_pos : c1;
+    // the last segment at or before the oldest position a later frame can ask for, and every later one
+    const long long seg_keep = (npend ? pend[0] : c1) - 1;
+    int ks = 0;
+    for (int a = 0; a < nseg; a++) if (segs[a].t <= seg_keep) ks = a;
+    st.nsegc = 0;
+    for (int a = ks; a < nseg; a++) { if (st.nsegc < DTL_SYNC_SEGC) st.segc[st.nsegc++] = segs[a]; else err = 1; }
+    st.base_cur = base; st.len_cur = len;
+    p.st[s] = st;
+    if (err) atomicOr(p.err, err == 2 ? 64 : 1024);
+}
+
+// Frame j of stream s: out[q] = x[t + q - D] * exp(j phase[t + q]).  Unused frame slots are zero-filled and flagged invalid.
+__global__ void __launch_bounds__(256) sync_cut_kernel(SyncParams p)
+{
+    const int s = blockIdx.z, j = blockIdx.y;
+    const int FS = p.FS, N = p.N, D = N + p.cp;
+    float2* out = p.frames + ((size_t)s * p.frames_cap + j) * FS;
+    const int nfr = p.n_frames[s];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        p.valid[(size_t)s * p.frames_cap + j] = j < nfr;
+        if (p.starts_out) p.starts_out[(size_t)s * p.frames_cap + j] = j < nfr ? p.starts[(size_t)s * p.frames_cap + j] : -1;
+    }
+    const int q0 = blockIdx.x * 1024;
+    if (j >= nfr) {
+        for (int q = q0 + threadIdx.x; q < min(q0 + 1024, FS); q += blockDim.x) out[q] = make_float2(0.f, 0.f);
+        return;
+    }
+    const SyncState& st = p.st[s];                               // after sync_scan_kernel: base_prev / len of THIS call's buffer
+    const long long base = st.base_cur, t = p.starts[(size_t)s * p.frames_cap + j];
+    const int len = st.len_cur, nseg = p.n_seg[s];
+    const float2* w = p.w_new + (size_t)s * p.w_cap;
+    const SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;
+    for (int q = q0 + threadIdx.x; q < min(q0 + 1024, FS); q += blockDim.x) {
+        const float2 y = ld_w(w, t + q - D, base, len);
+        const double ph = sync_phase(segs, nseg, t + q, N);
+        double sn, cs;
+        sincos(ph, &sn, &cs);
+        const float c = (float)cs, sf = (float)sn;
+        out[q] = make_float2(__fmaf_rn(y.x, c, -__fmul_rn(y.y, sf)), __fmaf_rn(y.x, sf, __fmul_rn(y.y, c)));
+    }
+}
+
+__global__ void sync_reset_kernel(SyncState* st, int n)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    SyncState z;
+    memset(&z, 0, sizeof z);
+    st[s] = z;
+}
+
+cudaError_t launch_sync_reset(cudaStream_t st, SyncState* state, int n)
+{
+    if (n <= 0) return cudaSuccess;
+    sync_reset_kernel<<<(n + 255) / 256, 256, 0, st>>>(state, n);
+    return cudaGetLastError();
+}
+
+size_t sync_metric_smem(int N) { const int T = N > 1024 ? N : 1024; return (size_t)(T + N + N / 2) * 8 + 3 * (size_t)(T + N) * 8 + 3 * (size_t)(T + N) * 4; }
+
+cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches)
+{
+    if (p.n_streams <= 0 || p.T <= 0) return cudaSuccess;
+    const int max_len = p.w_cap;
+    sync_append_kernel<<<dim3((unsigned)((max_len + 2047) / 2048 < 64 ? (max_len + 2047) / 2048 : 64), p.n_streams), 256, 0, st>>>(p);
+    const int tiles = (int)((p.T + p.keep_cap + 1023) / 1024 + 1);
+    sync_metric_kernel<1024><<<dim3(tiles, p.n_streams), 256, sync_metric_smem(p.N), st>>>(p);
+    sync_scan_kernel<<<(p.n_streams + 63) / 64, 64, 0, st>>>(p);
+    sync_cut_kernel<<<dim3((p.FS + 1023) / 1024, p.frames_cap, p.n_streams), 256, 0, st>>>(p);
+    if (launches) *launches += 4;
+    return cudaGetLastError();
+}
+
+cudaError_t init_kernels_sync() { return set_max_dyn_smem(sync_metric_kernel<1024>); }
+
+} // namespace dtl

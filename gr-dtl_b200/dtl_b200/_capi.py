@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("DTL_B200_LIB") or os.path.join(os.path.dirname(_HERE)
 OK, ERR_INVALID_ARG, ERR_MISSING_TAG, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED, ERR_CAPACITY, ERR_IO = range(8)
 MEM_HOST, MEM_DEVICE = 0, 1
 LDPC_REFERENCE, LDPC_LAYERED = 0, 1
-STAGES = ("fft", "eq_demap", "stream_state", "tb_plan", "ldpc", "tb_finish", "tx", "demap", "header")
+STAGES = ("fft", "eq_demap", "stream_state", "tb_plan", "ldpc", "tb_finish", "tx", "demap", "header", "sync")
 
 frame_meta_dtype = np.dtype([
     ("constellation", "<i4"), ("carrier_offset", "<i4"), ("frame_no", "<i4"), ("payload_len", "<i4"),
@@ -44,10 +44,10 @@ class dtl_config(C.Structure):
         ("fec_enabled", C.c_int32), ("max_bps", C.c_int32), ("ldpc_max_iterations", C.c_int32),
         ("ldpc_mode", C.c_int32), ("ldpc_sigma2", C.c_double),
         ("sync_word1", _f32p), ("sync_word2", _f32p),
-        ("device", C.c_int32), ("reserved", C.c_int32 * 7)]
+        ("device", C.c_int32), ("sync_threshold", C.c_float), ("reserved", C.c_int32 * 6)]
 
 
-# every symbol include/dtl_b200.h declares (tests/test_capi_symbols.py checks the header against this list)
+# every symbol include/dtl_b200.h declares (tests/test_capi_cpu.py checks the header and the built library against this list)
 SYMBOLS = (
     "dtl_b200_abi_version", "dtl_b200_create", "dtl_b200_destroy", "dtl_b200_last_error", "dtl_b200_reset",
     "dtl_b200_sync", "dtl_b200_cuda_stream", "dtl_b200_frame_capacity", "dtl_b200_frame_samples",
@@ -55,7 +55,7 @@ SYMBOLS = (
     "dtl_b200_profile", "dtl_b200_stage_times",
     "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize",
     "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode",
-    "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq", "dtl_b200_fec_frame")
+    "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq", "dtl_b200_fec_frame", "dtl_b200_rx_stream")
 
 _lib = None
 
@@ -110,5 +110,6 @@ def lib():
         L.dtl_b200_fec_frame.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, vp, vp, vp, vp, C.c_int]
         L.dtl_b200_rx_headers.argtypes = [vp, vp, i32, i32, vp, vp, vp, C.c_int]
         L.dtl_b200_rx_iq.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
+        L.dtl_b200_rx_stream.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp, i32, vp, vp, C.c_int]
         _lib = L
     return _lib

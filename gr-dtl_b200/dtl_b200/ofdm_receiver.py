@@ -115,6 +115,7 @@ class ofdm_receiver:
         cfg.ldpc_max_iterations, cfg.ldpc_mode, cfg.ldpc_sigma2 = ldpc_max_iterations, ldpc_mode, ldpc_sigma2
         cfg.sync_word1, cfg.sync_word2 = f32(config.sync_word1), f32(config.sync_word2)
         cfg.device = device
+        cfg.sync_threshold = float(getattr(config, "sync_threshold", 0.95))
         self._keep = keep
         h = C.c_void_p()
         st = self._lib.dtl_b200_create(C.byref(cfg), C.byref(h))
@@ -213,7 +214,7 @@ class ofdm_receiver:
             torch.cuda.current_stream(t.device).synchronize()
             return t
         tdt = {np.dtype(np.float32): torch.float32, np.dtype(np.complex64): torch.complex64, np.dtype(np.uint8): torch.uint8,
-               np.dtype(np.int32): torch.int32, np.dtype(np.float64): torch.float64}[np.dtype(dtype)]
+               np.dtype(np.int32): torch.int32, np.dtype(np.float64): torch.float64, np.dtype(np.int64): torch.int64}[np.dtype(dtype)]
         t = torch.zeros(shape, dtype=tdt, device="cuda:%d" % self.device)
         # the fill runs on torch's current stream, the library works on its own: without this a large fill can land
         # after (on top of) what the library's kernels wrote
@@ -359,6 +360,31 @@ class ofdm_receiver:
         g = lambda k: _Arg(o.get(k)).ptr
         self._ck(self._lib.dtl_b200_rx_iq(self._h, a.ptr, S, F, g("meta"), g("hres"), g("res"), g("bytes"), bytes_cap,
                                           g("nbytes"), g("tbs"), tb_cap, g("ntbs"), g("frame_crc"), mem))
+        return o
+
+    def rx_stream(self, iq, n_streams, frames_cap, bytes_cap=None, tb_cap=None, want_frames=False):
+        """The receive path from CONTINUOUS IQ (python/dtl/ofdm_receiver.py:70-97 in front of the header and payload branches):
+        Schmidl & Cox synchroniser, fine-CFO mixer, trigger regulariser, then rx_iq on the frames found.  iq: [S, T] the next T
+        samples of every stream (state is kept between calls).  Returns the rx_iq outputs for S x frames_cap frame slots plus
+        n_frames [S] and frame_start [S * frames_cap] (-1 = empty slot)."""
+        from ._capi import header_result_dtype
+        S, F = int(n_streams), int(frames_cap)
+        a = _Arg(iq)
+        mem = a.mem
+        T = (iq.numel() if _is_torch(iq) else iq.size) // S
+        bytes_cap = bytes_cap or (self.bytes_stride + 8) * (F + 1)
+        tb_cap = tb_cap or 2 * F + 1
+        o = dict(res=self._new(mem, (S * F,), frame_result_dtype), bytes=self._new(mem, (S, bytes_cap), np.uint8),
+                 nbytes=self._new(mem, (S,), np.int32), tbs=self._new(mem, (S, tb_cap), tb_result_dtype),
+                 ntbs=self._new(mem, (S,), np.int32), frame_crc=self._new(mem, (S * F,), np.int32),
+                 meta=self._new(mem, (S * F,), frame_meta_dtype), hres=self._new(mem, (S * F,), header_result_dtype),
+                 n_frames=self._new(mem, (S,), np.int32), frame_start=self._new(mem, (S * F,), np.int64))
+        if want_frames:
+            o["frames"] = self._new(mem, (S * F, self.frame_samples), np.complex64)
+        g = lambda k: _Arg(o.get(k)).ptr
+        self._ck(self._lib.dtl_b200_rx_stream(self._h, a.ptr, S, T, F, g("n_frames"), g("frame_start"), g("frames"), g("meta"),
+                                              g("hres"), g("res"), g("bytes"), bytes_cap, g("nbytes"), g("tbs"), tb_cap,
+                                              g("ntbs"), g("frame_crc"), mem))
         return o
 
     # ---- the whole payload branch ------------------------------------------------------------------------------

@@ -115,7 +115,8 @@ typedef struct dtl_config {
     double ldpc_sigma2;                 /* awgn_bp sigma^2; the reference never sets it -- 2.0 = "LLR in" */
     const float* sync_word1; const float* sync_word2;   /* [fft_len] re,im shifted layout; TX only, may be NULL */
     int32_t device;                     /* CUDA device ordinal */
-    int32_t reserved[7];
+    float sync_threshold;               /* digital.ofdm_sync_sc_cfb threshold (config.py:56; <= 0: 0.95) -- dtl_b200_rx_stream only */
+    int32_t reserved[6];
 } dtl_config;
 
 typedef struct dtl_b200 dtl_b200;
@@ -147,7 +148,7 @@ uint64_t dtl_b200_launch_count(const dtl_b200* h);
  * stream; dtl_b200_stage_times waits for the stream and returns, per stage, the accumulated milliseconds and
  * the number of kernel launches since the last reset (ms / launches may be NULL; n <= DTL_STAGE_COUNT). */
 enum { DTL_STAGE_FFT = 0, DTL_STAGE_EQ = 1, DTL_STAGE_STATE = 2, DTL_STAGE_TBPLAN = 3, DTL_STAGE_LDPC = 4,
-       DTL_STAGE_TBFINISH = 5, DTL_STAGE_TX = 6, DTL_STAGE_DEMAP = 7, DTL_STAGE_HEADER = 8, DTL_STAGE_COUNT = 9 };
+       DTL_STAGE_TBFINISH = 5, DTL_STAGE_TX = 6, DTL_STAGE_DEMAP = 7, DTL_STAGE_HEADER = 8, DTL_STAGE_SYNC = 9, DTL_STAGE_COUNT = 10 };
 dtl_status dtl_b200_profile(dtl_b200* h, int enable);
 dtl_status dtl_b200_stage_times(dtl_b200* h, double* ms, int64_t* launches, int32_t n, int reset);
 /* Page-locked host memory for DTL_MEM_HOST buffers (what a GNU Radio custom buffer would hand to work()):
@@ -284,6 +285,25 @@ dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_streams, int32
                           dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
                           uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
                           dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem);
+
+/* ---- synchronisation front end + the receive path: continuous IQ in, payload bytes out ------
+ * python/dtl/ofdm_receiver.py:70-97: digital.ofdm_sync_sc_cfb(fft_len, cp_len, threshold) (Schmidl & Cox timing metric, plateau
+ * detector, fine frequency estimate), blocks.delay(fft_len + cp_len) + analog.frequency_modulator_fc(-2 / fft_len) +
+ * blocks.multiply_cc (fine CFO removed), dtl.ofdm_adaptive_frame_detect_bb (lib/dtl/ofdm_adaptive_frame_detect_bb_impl.cc:64-156,
+ * trigger regulariser) and the trigger input of digital.header_payload_demux; then dtl_b200_rx_iq on the frames found.
+ *   iq          c64 [S][samples_per_stream] (in): the next samples of S continuous streams.  Detector, oscillator, regulariser
+ *               and the samples a later call still needs are per-stream state (cleared by dtl_b200_reset); one call = one
+ *               work() call of the regulariser (its output depends on the chunking, as in the reference).
+ *   frames_cap  F: frame slots per stream in every per-frame output; frames completed by this call fill slots 0..n_frames[s]-1,
+ *               the other slots are reported as dropped frames (meta.reserved = 1).  More than F frames: DTL_ERR_CAPACITY.
+ *   n_frames [S] (out), frame_start i64 [S*F] (out, nullable): position of each frame's first sample in the stream, -1 = empty
+ *   frames_out  c64 [S*F][frame_samples] (out, nullable): the frames as header_payload_demux receives them
+ * The first call after dtl_b200_reset fixes the largest samples_per_stream later calls may use. */
+dtl_status dtl_b200_rx_stream(dtl_b200* h, const float* iq, int32_t n_streams, int64_t samples_per_stream, int32_t frames_cap,
+                              int32_t* n_frames, int64_t* frame_start, float* frames_out,
+                              dtl_frame_meta* meta_out, dtl_header_result* hres, dtl_frame_result* res,
+                              uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
+                              dtl_tb_result* tbs, int32_t tb_cap, int32_t* ntbs, int32_t* frame_crc, int mem);
 
 #ifdef __cplusplus
 }

@@ -397,6 +397,35 @@ class Config:
         return out
 
 
+class StreamSync:
+    """Synchronisation front end of one continuous IQ stream (oracle/src/sync.cc): push(chunk) -> frames cut at the
+    regularised Schmidl & Cox triggers, fine CFO removed."""
+
+    def __init__(self, cfg, threshold=0.95):
+        self.cfg = cfg
+        f = lib().orc_sync_create
+        f.restype = C.c_void_p
+        self.h = C.c_void_p(f(cfg.h, C.c_float(threshold)))
+
+    def push(self, x, frame_cap=64, trig_cap=256):
+        x = _c64_as_f32(x)
+        fs = self.cfg.frame_samples
+        frames = np.zeros((frame_cap, fs), dtype=np.complex64)
+        starts = np.zeros(frame_cap, dtype=np.int64)
+        raw, fixed = np.zeros(trig_cap, dtype=np.int64), np.zeros(trig_cap, dtype=np.int64)
+        nr, nf = C.c_int(0), C.c_int(0)
+        n = lib().orc_sync_push(self.h, _p(x), x.size, _p(frames), _p(starts), frame_cap, _p(raw), C.byref(nr), _p(fixed),
+                                C.byref(nf), trig_cap)
+        if n > frame_cap:
+            raise RuntimeError("frame_cap too small")
+        return dict(frames=frames[:n].copy(), starts=starts[:n].copy(), raw=raw[:nr.value].copy(), fixed=fixed[:nf.value].copy())
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_sync_destroy(self.h)
+            self.h = None
+
+
 class FrameEqualizer:
     def __init__(self, cfg, literal=False, symbols_skipped=None, alpha=0.1):
         self.cfg = cfg

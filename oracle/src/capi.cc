@@ -420,6 +420,29 @@ int orc_rx_headers(void* cfgh, const float* iq, int S, int F, int nthreads, fram
     return 0;
 }
 
+// ---- synchronisation front end (sync.cc) ------------------------------------------------------------------------------
+void* orc_sync_create(void* cfgh, float threshold)
+{
+    const stream_cfg& cfg = ((cfg_box*)cfgh)->c;
+    return new stream_sync(cfg.ofdm.fft_len, cfg.ofdm.cp_len, cfg.frame_samples(), threshold);
+}
+void orc_sync_destroy(void* h) { delete (stream_sync*)h; }
+// one chunk of T samples; returns the number of frames completed (<= frame_cap), their samples in frames[n][FS], their start
+// positions in starts; raw / fixed: trigger positions of this chunk (counts in n_raw / n_fixed, capacity trig_cap)
+int orc_sync_push(void* h, const float* x, int T, float* frames, long long* starts, int frame_cap,
+                  long long* raw, int* n_raw, long long* fixed, int* n_fixed, int trig_cap)
+{
+    stream_sync* s = (stream_sync*)h;
+    std::vector<cf32> fr; std::vector<long long> st, rw, fx;
+    s->push((const cf32*)x, T, fr, st, &rw, &fx);
+    const int n = std::min((int)st.size(), frame_cap);
+    if (frames) memcpy(frames, fr.data(), (size_t)n * s->FS * sizeof(cf32));
+    for (int i = 0; i < n; i++) starts[i] = st[i];
+    if (n_raw) { *n_raw = std::min((int)rw.size(), trig_cap); for (int i = 0; i < *n_raw; i++) raw[i] = rw[i]; }
+    if (n_fixed) { *n_fixed = std::min((int)fx.size(), trig_cap); for (int i = 0; i < *n_fixed; i++) fixed[i] = fx[i]; }
+    return (int)st.size();
+}
+
 void orc_rx_demod(void* cfgh, const float* iq, int count, float* out)
 {
     const stream_cfg& cfg = ((cfg_box*)cfgh)->c;

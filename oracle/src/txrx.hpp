@@ -63,6 +63,25 @@ struct rx_header {
     bool frame(const cf32* iq, frame_meta* m, cf32* taps_out, int* fb_cnst, int* fb_fec);
 };
 
+// synchronisation front end (python/dtl/ofdm_receiver.py:70-97; sync.cc): one instance per continuous IQ stream
+struct stream_sync {
+    struct seg { long long t; double ph; float f; };       // oscillator: phase[t] = ph, slope -2/N * f from t on
+    int N, cp, FS; float threshold;
+    std::vector<cf32> buf; long long base = 0, total = 0, scan_pos = 0, chunk_pos = 0, busy_until = 0;
+    std::vector<seg> segs; std::vector<long long> pending;
+    // ofdm_adaptive_frame_detect_bb_impl members
+    int d_remainder = 0, d_missing_count = 0, d_correction_count = 0, d_acc_error = 0, d_trigger_counter = 0, d_synced = 0,
+        d_error_count = 0;
+    bool d_in_sync = false;
+    stream_sync(int fft_len, int cp_len, int frame_samples, float thr);
+    cf32 x_at(long long n) const;
+    void metric_at(long long n, float* m, cf32* p) const;
+    double phase_at(long long n) const;
+    std::vector<long long> fix_sync(long long c0, long long c1, const std::vector<long long>& trig);
+    void push(const cf32* x, int T, std::vector<cf32>& frames, std::vector<long long>& starts,
+              std::vector<long long>* raw_out = nullptr, std::vector<long long>* fixed_out = nullptr);
+};
+
 struct rx_frame_out {
     frame_result res; const cf32* hard = nullptr; const cf32* soft = nullptr;
     const float* llr = nullptr; int n_llr = 0; int crc_ok = -1;
