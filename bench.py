@@ -621,7 +621,7 @@ def run_b200(a):
     eq_ms = eq["ms_per_step"]
     achieved = alg["eq_demap"] * frames / (eq_ms * 1e-3) / 1e9
     tr = facts.get("eq_fast_kernel", {}).get("dram_bytes_per_frame")
-    roofline = {"kernel": "eq_fast_kernel + snr_tags_kernel (frame equaliser + serialiser + soft demapper + sign words; whole stage timed)",
+    roofline = {"kernel": "eq_fast_kernel (frame equaliser + serialiser + soft demapper + sign words; CUDA events around the kernel on the library stream)",
                 "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None if tr is None else tr * frames,
                 "alg_bytes_per_launch": alg["eq_demap"] * frames, "ms_per_launch": eq_ms, "peak_source": peak_src}

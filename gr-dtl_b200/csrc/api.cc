@@ -934,7 +934,7 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
     bool tags_due = false;
     if (h->hdr_pending) { h->hdr_pending = false; CK(cudaStreamWaitEvent(h->stream, h->ev_hdr, 0)); }   // tags + taps come from the side stream
     h->prof.begin(DTL_STAGE_EQ, 1);
-    CK(launch_eq(h->stream, p, &eq_launches, ov ? &tags_due : nullptr));
+    CK(launch_eq(h->stream, p, &eq_launches, &tags_due));       // the fast kernel leaves the SNR tags to snr_tags_kernel, launched below
     if (sgn && !eq_emits_signs(p)) {             // the general kernel / tiny FFTs: sign words by a pass over the LLRs
         CK(launch_llr_sign(h->stream, llr, h->llr_stride, n, sgn, h->sgn_stride));
         eq_launches++;
@@ -945,17 +945,17 @@ dtl_status dev_equalize(dtl_b200* h, Stage& sg, const float2* freq, const float2
         CK(cudaEventRecord(h->ev_eq, h->stream));
         CK(cudaStreamWaitEvent(h->side_stream, h->ev_eq, 0));
         ss = h->side_stream;
-        if (tags_due) CK(launch_snr_tags(ss, p));
     }
     StreamParams sp;
     sp.st = (StreamState*)h->st_buf.p + h->s_off; sp.n_streams = S; sp.F = F; sp.meta = meta; sp.res = res;
     sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
     sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
-    h->prof.begin(DTL_STAGE_STATE, 1);
+    h->prof.begin(DTL_STAGE_STATE, tags_due ? 2 : 1);           // tags + feedback decision: the per-frame / per-stream bookkeeping stage
+    if (tags_due) CK(launch_snr_tags(ss, p));
     CK(launch_stream_state(ss, sp));
     h->prof.end();
     if (ov) { CK(cudaEventRecord(h->ev_side, h->side_stream)); h->side_pending = true; }
-    h->launches += eq_launches + 1;
+    h->launches += eq_launches + 1 + (tags_due ? 1 : 0);
     return DTL_OK;
 }
 

@@ -223,6 +223,87 @@ __global__ void __launch_bounds__(256) tx_mod_kernel(TxParams p)
     }
 }
 
+// ---- N = 1024 (SURVEY.md section 8d configuration 5): 32 x 32 decomposition, ONE WARP per symbol, 32 points per lane ------
+// n = n0 + 32 n1, k = k1 + 32 k2:  X[k1 + 32 k2] = sum_n0 W32^(n0 k2) . W1024^(n0 k1) . sum_n1 x[n0 + 32 n1] W32^(n1 k1).
+// Lane n0 loads x[n0 + 32 n1] (every load instruction of the warp is one contiguous 256-byte run), does the inner 32-point
+// DFT in registers (radix-2 decimation in frequency, fully unrolled: twiddles are immediates, the bit-reversed result order
+// is resolved at compile time), applies W1024^(n0 k1) from the table, and the warp transposes through its own 8.25 KB of
+// shared memory ONCE (row stride 33: both sides conflict-free; __syncwarp only); lane k1 then does the outer 32-point DFT
+// and stores X[k1 + 32 k2] -- again 256 contiguous bytes per instruction.  No CTA barrier, no staging of input or output:
+// HBM traffic is the algorithmic 16 N bytes per symbol.
+__device__ __forceinline__ constexpr float cos32(int k)             // cos(2 pi k / 32), k = 0 .. 16
+{
+    constexpr float t[17] = { 1.0f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f, 0.70710678118654752f,
+                              0.55557023301960218f, 0.38268343236508977f, 0.19509032201612825f, 0.0f, -0.19509032201612825f,
+                              -0.38268343236508977f, -0.55557023301960218f, -0.70710678118654752f, -0.83146961230254524f,
+                              -0.92387953251128674f, -0.98078528040323043f, -1.0f };
+    return t[k];
+}
+__device__ __forceinline__ constexpr float sin32(int k) { return k <= 8 ? cos32(8 - k) : cos32(k - 8); }      // sin(2 pi k / 32), k = 0 .. 16
+// d * W32^k (forward: exp(-2 pi i k / 32)), k a compile-time constant after unrolling
+__device__ __forceinline__ float2 mul_w32(float2 d, int k)
+{
+    if (k == 0) return d;
+    if (k == 8) return make_float2(d.y, -d.x);
+    const float c = cos32(k), sn = sin32(k);
+    return make_float2(d.x * c + d.y * sn, d.y * c - d.x * sn);
+}
+__device__ __forceinline__ constexpr int bitrev5(int i) { return ((i & 1) << 4) | ((i & 2) << 2) | (i & 4) | ((i & 8) >> 2) | ((i & 16) >> 4); }
+// in place, natural order in, X[bitrev5(i)] in x[i] out
+__device__ __forceinline__ void dft32_fwd(float2 (&x)[32])
+{
+#pragma unroll
+    for (int half = 16; half >= 1; half >>= 1) {
+#pragma unroll
+        for (int base = 0; base < 32; base += 2 * half) {
+#pragma unroll
+            for (int j = 0; j < half; j++) {
+                const float2 a = x[base + j], b = x[base + j + half];
+                x[base + j] = make_float2(a.x + b.x, a.y + b.y);
+                x[base + j + half] = mul_w32(make_float2(a.x - b.x, a.y - b.y), j * (16 / half));
+            }
+        }
+    }
+}
+
+#define DTL_FFT1K_WARPS 4
+#define DTL_FFT1K_ROW 33
+__global__ void __launch_bounds__(DTL_FFT1K_WARPS * 32, 4) fft1024_fwd_kernel(const float2* __restrict__ in, float2* __restrict__ out,
+                                                                             unsigned n_sym, unsigned syms_per_frame, long long in_frame_stride,
+                                                                             int in_sym0, int in_sym_stride, int in_skip,
+                                                                             const float2* __restrict__ tw)
+{
+    extern __shared__ float2 sm[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float2* xs = sm + (size_t)w * 32 * DTL_FFT1K_ROW;
+    const unsigned step = gridDim.x * DTL_FFT1K_WARPS;
+    for (unsigned q = blockIdx.x * DTL_FFT1K_WARPS + w; q < n_sym; q += step) {
+        const unsigned fr = q / syms_per_frame, i = q - fr * syms_per_frame;
+        const float2* src = in + fr * in_frame_stride + (long long)(in_sym0 + (int)i) * in_sym_stride + in_skip;
+        float2 x[32];
+#pragma unroll
+        for (int r = 0; r < 32; r++) x[r] = __ldcs(&src[lane + 32 * r]);
+        dft32_fwd(x);
+#pragma unroll
+        for (int r = 0; r < 32; r++) {                          // x[r] = A[k1], k1 = bitrev5(r): twiddle W1024^(lane k1), row k1, column lane
+            const int k1 = bitrev5(r);
+            const float2 v = k1 ? cmul(x[r], __ldg(&tw[lane * k1])) : x[r];
+            xs[k1 * DTL_FFT1K_ROW + lane] = v;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int n0 = 0; n0 < 32; n0++) x[n0] = xs[lane * DTL_FFT1K_ROW + n0];
+        __syncwarp();
+        dft32_fwd(x);
+        float2* dst = out + (size_t)q * 1024;
+#pragma unroll
+        for (int r = 0; r < 32; r++) {                          // x[r] = X[lane + 32 k2], k2 = bitrev5(r); out[(k + 512) % 1024] = X[k]
+            const int k2 = bitrev5(r);
+            dst[lane + 32 * ((k2 + 16) & 31)] = x[r];
+        }
+    }
+}
+
 // ---- launchers -------------------------------------------------------------------------------------------
 static inline int ilog2(int n) { int l = 0; while ((1 << l) < n) l++; return l; }
 
@@ -236,6 +317,15 @@ cudaError_t launch_fft_fwd(cudaStream_t st, const float2* in, float2* out, long 
         const long long need = (n_sym + 31) / 32, cap = (long long)sms * 4 * 4;       // 4 resident CTAs per SM (59 registers), 4 waves
         fft64_fwd_kernel<<<(unsigned)(need < cap ? need : cap), 256, 0, st>>>(in, out, (unsigned)n_sym, (unsigned)syms_per_frame,
                                                                            in_frame_stride, in_sym0, in_sym_stride, in_skip, tw);
+        return cudaGetLastError();
+    }
+    if (N == 1024 && n_sym < 0x7fffffffLL && syms_per_frame > 0) {
+        static int sms = 0;
+        if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        const long long need = (n_sym + DTL_FFT1K_WARPS - 1) / DTL_FFT1K_WARPS, cap = (long long)sms * 4 * 8;   // 4 resident CTAs per SM, 8 waves
+        const size_t smem = (size_t)DTL_FFT1K_WARPS * 32 * DTL_FFT1K_ROW * sizeof(float2);
+        fft1024_fwd_kernel<<<(unsigned)(need < cap ? need : cap), DTL_FFT1K_WARPS * 32, smem, st>>>(
+            in, out, (unsigned)n_sym, (unsigned)syms_per_frame, in_frame_stride, in_sym0, in_sym_stride, in_skip, tw);
         return cudaGetLastError();
     }
     const int T = N / 4, threads = T >= 256 ? T : 256, G = threads / T;
@@ -272,6 +362,7 @@ cudaError_t init_kernels_fft()
     cudaError_t e = set_max_dyn_smem(fft_fwd_kernel);
     if (e == cudaSuccess) e = set_max_dyn_smem(fft_inv_kernel);
     if (e == cudaSuccess) e = set_max_dyn_smem(tx_mod_kernel);
+    if (e == cudaSuccess) e = set_max_dyn_smem(fft1024_fwd_kernel);
     return e;
 }
 

@@ -39,9 +39,12 @@ ofdm_adaptive_payload_equalizer::sptr ofdm_adaptive_payload_equalizer::make(
     if (!snr_est) throw std::invalid_argument("SNR estimator missing");
     if (dynamic_cast<ofdm_adaptive_frame_snr_simple*>(snr_est.get()) == nullptr)
         throw std::invalid_argument("libdtl_b200 implements ofdm_adaptive_frame_snr_simple only");
-    if (pilot_carriers.size() != pilot_symbols.size()) throw std::invalid_argument("pilot carriers and symbols do not match");   // digital::ofdm_equalizer_1d_pilots ctor
-    for (size_t i = 0; i < pilot_carriers.size(); i++)
-        if (pilot_carriers[i].size() != pilot_symbols[i].size()) throw std::invalid_argument("pilot carriers and symbols do not match");
+    // digital::ofdm_equalizer_1d_pilots ctor: symbol set i goes with carrier set (symbols_skipped + i) % n_carrier_sets
+    for (size_t i = 0; i < pilot_symbols.size(); i++) {
+        if (pilot_carriers.empty()) throw std::invalid_argument("pilot symbols without pilot carriers");
+        if (pilot_carriers[(symbols_skipped + i) % pilot_carriers.size()].size() != pilot_symbols[i].size())
+            throw std::invalid_argument("pilot carriers and symbols do not match");
+    }
     sptr e(new ofdm_adaptive_payload_equalizer());
     e->d_self = e;
     e->d_fft_len = fft_len; e->d_cnsts = constellations; e->d_symbols_skipped = symbols_skipped; e->d_alpha = alpha;
