@@ -224,6 +224,60 @@ def alg_bytes(N, L, cap, bps, fec):
     return {"fft": fft, "eq_demap": eq}
 
 
+def numa_bind(torch, local):
+    """Pin this rank's threads to the CPUs NVML names as closest to its GPU (the socket / NUMA node its PCIe root hangs off),
+    so that the page-locked staging buffers of the e2e legs are allocated on that node and the feeding thread runs there."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(local).uuid)
+        uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+        try:
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+        before = len(os.sched_getaffinity(0))
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        cpus = sorted(os.sched_getaffinity(0))
+        node = None
+        try:
+            bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+            bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+            with open("/sys/bus/pci/devices/%s/numa_node" % bus[-12:]) as f:
+                node = int(f.read().strip())
+        except Exception:
+            pass
+        return {"bound": True, "cpus": len(cpus), "cpus_before": before, "first_cpu": cpus[0], "node": node}
+    except Exception as e:                                   # no NVML / not permitted: run unpinned and say so
+        return {"bound": False, "why": str(e)[:80]}
+
+
+def h2d_ceiling(ctx, mb=256, reps=6):
+    """What the box gives every GPU when ALL ranks copy page-locked host memory to their device at the same time (the e2e
+    legs cannot beat this): barrier, `reps` copies of `mb` MB per rank, max time over ranks."""
+    torch = ctx.torch
+    n = mb << 20
+    h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h.fill_(1)
+    d = torch.empty(n, dtype=torch.uint8, device=ctx.dev)
+    d.copy_(h, non_blocking=True)
+    ctx.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        d.copy_(h, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(ctx.dev)
+    ms = e0.elapsed_time(e1)
+    worst = ctx.reduce(ms, "MAX")
+    mean = ctx.reduce(ms, "SUM") / ctx.world
+    ctx.barrier()
+    del h, d
+    return {"h2d_gbs_per_gpu": reps * n / (worst * 1e-3) / 1e9, "h2d_gbs_per_gpu_mean": reps * n / (mean * 1e-3) / 1e9,
+            "concurrent_gpus": ctx.world, "mb_per_copy": mb, "copies": reps,
+            "note": "all ranks copying at once from page-locked memory allocated after NUMA binding; slowest rank"}
+
+
 class Ctx:
     """what every leg needs: device, barrier / reductions over the ranks, the event-timed loop"""
 
@@ -235,6 +289,8 @@ class Ctx:
         self.local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(self.local)
         self.dev = torch.device("cuda:%d" % self.local)
+        self.cpus_all = os.sched_getaffinity(0)
+        self.numa = numa_bind(torch, self.local)       # before any page-locked buffer exists: first touch is NUMA-local then
         self.dist = None
         if self.world > 1:
             import torch.distributed as dist
@@ -435,8 +491,9 @@ def run_b200(a):
                  "seconds": ms_sus * n_sus * 1e-3, "clocks": clocks_sus}
 
     # ---- end to end through the C ABI with HOST buffers (H2D of the inputs + D2H of the results inside the timing)
-    e2e = e2e_iq = None
+    e2e = e2e_iq = ceiling = None
     if not a.no_e2e:
+        ceiling = h2d_ceiling(ctx)
         h_iq = rx.host_alloc((S * F, fs), np.complex64)
         h_taps = rx.host_alloc((S * F, N), np.complex64)
         h_meta = rx.host_alloc((S * F,), dtl_b200.frame_meta_dtype)
@@ -470,7 +527,7 @@ def run_b200(a):
         d2h = sum(v.nbytes for v in h_out.values())
         e2e = {"value": samples_all / (ms_e2e * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e, "steps": k_e2e,
-               "h2d_gbs": h2d / (ms_e2e * 1e-3) / 1e9,
+               "h2d_gbs": h2d / (ms_e2e * 1e-3) / 1e9, "h2d_gbs_per_gpu_ceiling": ceiling["h2d_gbs_per_gpu"],
                "decoded_mbit_per_s": bits_all / (ms_e2e * 1e-3) / 1e6,
                "api": "dtl_b200_rx(mem=DTL_MEM_HOST) via dtl_b200.ofdm_receiver.rx, page-locked host buffers"}
         # the same from IQ alone: no taps / tags uploaded, the header branch derives them on the GPU
@@ -488,7 +545,7 @@ def run_b200(a):
         d2h2 = sum(v.nbytes for v in h_out2.values())
         e2e_iq = {"value": samples_all / (ms_e2e_iq * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h_iq.nbytes),
                   "d2h_bytes_per_step": int(d2h2), "ms_per_step": ms_e2e_iq, "steps": k_e2e,
-                  "h2d_gbs": h_iq.nbytes / (ms_e2e_iq * 1e-3) / 1e9,
+                  "h2d_gbs": h_iq.nbytes / (ms_e2e_iq * 1e-3) / 1e9, "h2d_gbs_per_gpu_ceiling": ceiling["h2d_gbs_per_gpu"],
                   "decoded_mbit_per_s": ctx.reduce(float(h_out2["nbytes"].sum()) * 8.0, "SUM") / (ms_e2e_iq * 1e-3) / 1e6,
                   "api": "dtl_b200_rx_iq(mem=DTL_MEM_HOST): host IQ only; channel taps and stream tags come from the frames' own "
                          "sync words and headers on the GPU"}
@@ -641,6 +698,10 @@ def run_b200(a):
                      "note": "iterations from the per-TB avg_it records (integer mean over the TB's 13 codewords): approximate"}
     cpu = None
     if not a.no_cpu_baseline:
+        try:
+            os.sched_setaffinity(0, ctx.cpus_all)        # the CPU leg uses every host core, not only the GPU's NUMA node
+        except OSError:
+            pass
         cpu = cpu_run(a, 8, 1, max_seconds=20.0)
         one = cpu_run(a, 3, 1, max_seconds=8.0, threads=1, streams=max(1, a.ref_streams // 16))
         cpu["single_thread"] = {kk: one[kk] for kk in ("value", "unit", "cores", "sample", "ms_per_step", "decoded_mbit_per_s")}
@@ -653,6 +714,7 @@ def run_b200(a):
         "config": config_dict(a, S),
         "verified": {"tbs_per_step_per_gpu": n_tbs, "crc_ok_tbs": int(ok_ref.sum()), "check": "decoded bytes == transmitted payload"},
         "e2e": e2e, "e2e_from_iq": e2e_iq, "sustained": sustained, "rx_from_iq": from_iq, "tx_fec_framer": tx_framer,
+        "h2d_ceiling": ceiling, "numa": ctx.numa,
         "gpu_launches": int(launches), "ms_per_step_serial": ms_serial, "clocks": clocks,
         "roofline": roofline, "roofline_ldpc": roofline_ldpc, "stages": stage_tab,
         "layered": layered, "latency": latency, "configs": configs, "cpu_baseline": cpu,

@@ -58,3 +58,38 @@ def test_mcs_stays_at_zero_when_the_estimate_is_below_every_threshold(fec):
     fb = got["res"]["fb_cnst"].reshape(S, 2 * F)
     assert (fb[:, :F] == orc.BPSK).all() and (fb[:, -1] == orc.QPSK).all()
     rx.close()
+
+
+def test_one_frame_per_call_120_consecutive_frames_match_the_oracle():
+    """The latency mode of a drop-in shim: S = 1, F = 1, DTL_MEM_HOST, one tagged frame per call.  120
+    consecutive frames of one stream, SNR low enough that BP iterates and some TBs fail: per-frame results, TB records and
+    payload equal the oracle's run over the same 120 frames (per-stream state -- TB reassembly across frames, feedback
+    counters, frame numbers -- lives in the handle between the calls)."""
+    import pyoracle as orc
+    from common import ALIST_300, make_oracle_cfg
+    ocfg = make_oracle_cfg(alists=(ALIST_300,), initial_mcs=1)
+    rx = make_receiver(alists=(ALIST_300,), initial_mcs=1)
+    F = 120
+    t = ocfg.tx_batch(1, F, seed=123, cnst=orc.QPSK, fec_id=1, snr_db=16.5)
+    freq = ocfg.rx_demod(t["iq"])
+    ref = ocfg.rx_batch(freq, t["taps"], t["meta"], 1, F, freq_domain=True)
+    fq = freq.reshape(F, ocfg.frame_len, 64)
+    rx.reset(1)
+    got_bytes, got_tbs = [], []
+    for j in range(F):
+        g = rx.rx(np.ascontiguousarray(fq[j:j + 1]), np.ascontiguousarray(t["taps"][j:j + 1]), t["meta"][j:j + 1].copy(), 1, 1,
+                  freq_domain=True)
+        for k in ("fb_cnst", "fb_fec", "emitted", "lost_frames"):
+            assert g["res"][k][0] == ref["res"][k][j], (k, j)
+        assert np.isclose(g["res"]["snr_db"][0], ref["res"]["snr_db"][j], rtol=1e-9)
+        got_bytes.append(g["bytes"][0, :g["nbytes"][0]].copy())
+        tb = g["tbs"][0, :g["ntbs"][0]].copy()
+        tb["frame_index"] += j                                   # frame index within the call -> within the run
+        got_tbs.append(tb)
+    tbs = np.concatenate(got_tbs)
+    r = ref["tbs"][0]
+    assert r["avg_it"].max() > 0 and (r["crc_ok"] == 0).any() and (r["crc_ok"] == 1).any(), "operating point not challenging"
+    for k in ("tb_no", "crc_ok", "nbytes", "avg_it"):
+        assert np.array_equal(tbs[k], r[k]), k
+    assert np.array_equal(np.concatenate(got_bytes), ref["bytes"][0])
+    rx.close()
