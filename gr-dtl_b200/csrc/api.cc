@@ -335,7 +335,7 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         }
     }
     // carrier-offset phase table (frame_equalizer_vcvc_impl.cc:168-177,189-193)
-    pl.max_off = std::min(N / 2, 256);
+    pl.max_off = N / 2;                                  // every offset ofdm_chanest_vcvc can report (|g| <= N/2)
     std::vector<float2> ptab((size_t)(2 * pl.max_off + 1) * (L + 1));
     for (int off = -pl.max_off; off <= pl.max_off; off++) {
         float2* row = &ptab[(size_t)(off + pl.max_off) * (L + 1)];
@@ -420,7 +420,12 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
         std::vector<float2> hrot((size_t)2 * pl.max_off + 1);
         for (int off = -pl.max_off; off <= pl.max_off; off++) hrot[(size_t)(off + pl.max_off)] = expj_contract((2.0 * M_PI) * off * h->cp / N * H);
         hd.ref = h->d_sync2; hd.corr_v = h->upload(corr, e); hd.kind = h->upload(hkind, e); hd.pinv = h->upload(hpinv, e);
-        hd.ser = h->upload(hser, e); hd.rot = h->upload(hrot, e);
+        // per-symbol phase of the HEADER symbols (frame_equalizer: -2 pi off cp / N (i + 1), i < H): its own table, the payload
+        // table's row has L + 1 entries and entry L is the channel-state rotation, not a symbol phase (H may exceed L)
+        std::vector<float2> hph((size_t)(2 * pl.max_off + 1) * H);
+        for (int off = -pl.max_off; off <= pl.max_off; off++)
+            for (int i = 0; i < H; i++) hph[(size_t)(off + pl.max_off) * H + i] = expj_contract(-(2.0 * M_PI) * off * h->cp / N * (i + 1));
+        hd.ser = h->upload(hser, e); hd.rot = h->upload(hrot, e); hd.hphase = h->upload(hph, e);
         // CRC-16 of the parser (ofdm_adaptive_packet_header.cc:99-111 pack_crc with its `i*len + j < header_len` bound, then
         // crc(16, 0x1021, 0xFFFF, 0, false, true)) as an affine map of the header bits: crc0 ^ XOR of crc_tab[j] over set bits
         {

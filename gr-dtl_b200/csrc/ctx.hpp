@@ -67,6 +67,7 @@ struct HdrDev {
     const float2* pinv;          // [H][N] 1 / pilot symbol (pilot-symbol set i % nps)
     const uint16_t* ser;         // [nbits] i*N + bin of header bit j (ofdm_serializer_vcc order, symbols_skipped 0)
     const float2* rot;           // [2*max_off+1] channel-state rotation exp(j 2 pi off cp/N H) after the header symbols
+    const float2* hphase;        // [2*max_off+1][H] per-symbol phase of the header symbols exp(-j 2 pi off cp/N (i+1))
     const uint16_t* crc_tab;     // [crc_bits] contribution of header bit j to the CRC-16 the parser computes (linear over GF(2))
     int crc_bits;                // bits pack_crc reads: 8 * ceil((nbits - 16) / 8)
     unsigned crc0;               // that CRC of an all-zero header

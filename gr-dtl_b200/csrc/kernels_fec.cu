@@ -7,18 +7,25 @@
 //   ldpc_dec::decode -> gr-fec awgn_bp::decode    lib/dtl/ldpc_dec.cc:62-71
 //   ofdm_adaptive_fec_pack_bb                     lib/dtl/ofdm_adaptive_fec_pack_bb_impl.cc:48-69
 //
-// Pipeline of one call (all on the handle's stream, nothing returns to the host in between):
-//   1. tb_plan_kernel     one thread per stream replays tb_decoder's frame-by-frame state machine on the
-//                         frame tags only, emitting for every released transport block (TB) the list of LLR
-//                         segments it is made of (carry buffer from earlier calls + ranges of this call's
-//                         frames) and one work item per codeword.
-//   2. ldpc_tb_kernel     persistent grid (CTAs = SMs x residency); each WARP pulls codeword work items from
-//                         a device counter, gathers its n LLRs (shortened positions = -15, tb_decoder.cc:145),
-//                         applies cldpc's column permutation, and decodes with messages in shared memory;
-//                         syndrome checks are warp votes, so a warp leaves as soon as its word converges.
-//   3. tb_finish_kernel   one warp per TB: bits -> bytes LSB-first (ballot), CRC-32 verify, mean iterations.
-//   4. tb_gather_kernel   one warp per stream: CRC-passing TBs' payload bytes concatenated in release order.
-//   5. carry_save_kernel  LLRs of the TB still in flight move to the per-stream carry buffer.
+// Pipeline of one call (on the handle's stream; the small tag-only kernels run on its side stream beside the heavy ones,
+// nothing returns to the host in between):
+//   1. tb_plan_kernel       one WARP per stream replays tb_decoder's frame-by-frame state machine on the frame tags only
+//                           (32 frames' tags per coalesced fetch, shuffled to every lane), emitting for every released
+//                           transport block (TB) the list of LLR segments it is made of (carry buffer from earlier calls +
+//                           ranges of this call's frames) and one work item per codeword.
+//   2. ldpc_screen_kernel   bit-sliced syndrome check of every codeword's hard decisions, read from the SIGN WORDS the
+//                           equaliser kernel writes next to the LLRs (1 bit per LLR); clean codewords leave here, the others
+//                           are queued on four lists by a coarse syndrome weight, hardest first.
+//   3. bp_gather_kernel     the queued codewords' LLRs -> one contiguous, wire-order block each (segments, shortened
+//                           positions = -15 of tb_decoder.cc:145, sign flip of ldpc_dec.cc:64-66).
+//   4. ldpc_bp_ref_kernel   (bp_ref.cuh; DTL_LDPC_REFERENCE) or ldpc_bp_lay_kernel (bp_layered.cuh; DTL_LDPC_LAYERED):
+//                           persistent grid, one codeword per warp from the queue, the NEXT codeword's block prefetched by a
+//                           TMA bulk copy; messages in shared memory; syndrome checks are warp votes, so a warp leaves as
+//                           soon as its word converges.  (ldpc_bp_kernel below is the slot-major decoder of round 1, kept for
+//                           codes without a row-major instance and for A/B: DTL_BP_OLD=1.)
+//   5. tb_finish_kernel     one warp per TB: bits -> bytes LSB-first, mean iterations.
+//   6. tb_gather_kernel     one CTA per stream: CRC-32 of its TBs, CRC-passing payload bytes concatenated in release order.
+//   7. carry_save_kernel    LLRs (and sign words) of the TB still in flight move to the per-stream carry buffer.
 //
 // Decoder flavours: DTL_LDPC_REFERENCE is gr-fec's awgn_bp restated operation by operation (flooding
 // sum-product on likelihood ratios, IEEE double, products in alist order) so payload bits AND iteration

@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) header_kernel(HdrParams p, int G, int gro
         }
         // ---- ofdm_frame_equalizer_vcvc: integer-offset shift of the flattened header symbols, zero fill, per-symbol phase
         if (shifted) {
-            const float2* ptab = p.pl.phase_tab + (size_t)(off + p.pl.max_off) * (p.pl.L + 1);
+            const float2* ptab = hd.hphase + (size_t)(off + p.pl.max_off) * H;
             const int total = H * N;
             for (int q = tid; q < total; q += T) {             // out[q] = in[q + off] (zero outside), times the phase of its symbol
                 const int j = q + off;

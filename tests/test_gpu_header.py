@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 import pyoracle as orc
-from common import ALIST_300, make_oracle_cfg, make_receiver
+from common import ALIST_300, ALIST_100_23, make_oracle_cfg, make_receiver
 
 pytestmark = pytest.mark.gpu
 
@@ -66,6 +66,25 @@ def test_header_branch_integer_carrier_offset(g):
         gb = full["bytes"][s, :full["nbytes"][s]]
         assert np.array_equal(gb, oref["bytes"][s]) and gb.size > 0
         assert np.array_equal(gb, t["payload"][s][:gb.size])
+    rx.close()
+
+
+@pytest.mark.parametrize("g", [-2, 4])
+def test_header_phase_when_the_header_is_longer_than_the_payload(g):
+    """frame_len = 1 with FEC: two header symbols, one payload symbol.  The header symbols' carrier-offset phases come from the
+    header's own table (the payload table of such a frame has one symbol entry; its next entry is the channel-state rotation)."""
+    ocfg = make_oracle_cfg(frame_len=1, cnsts=ALL, alists=(ALIST_100_23,))
+    rx = make_receiver(frame_len=1, cnsts=ALL, alists=(ALIST_100_23,))
+    assert ocfg.header_syms == 2 and ocfg.frame_len == 1
+    S, F = 3, 10
+    t = ocfg.tx_batch(S, F, seed=900 + g, cnst=5, fec_id=1, snr_db=36.0)          # 64QAM: one 48-carrier symbol holds a TB of the n = 100 code
+    fs = ocfg.frame_samples
+    rot = np.exp(2j * np.pi * g * np.arange(fs) / 64.0)
+    iq = (t["iq"].reshape(S * F, fs) * rot[None, :]).astype(np.complex64)
+    ref = ocfg.rx_headers(iq, S, F)
+    got = rx.rx_headers(iq, S, F)
+    assert ref["ok"].all() and np.all(ref["meta"]["carrier_offset"] == g)
+    _compare_headers(got, ref)
     rx.close()
 
 
