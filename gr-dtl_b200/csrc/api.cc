@@ -1103,6 +1103,46 @@ extern "C" dtl_status dtl_b200_equalize(dtl_b200* h, const float* freq, const fl
     return sg.finish();
 }
 
+// The lean equaliser pass for callers that must not allocate (include/dtl_b200.h).  Device pointers only; nothing here or below
+// calls cudaMalloc / cudaFree: no Stage (its scratch slots grow with cudaMalloc), no stream resize, the |pilot_eq| scratch is the
+// static device array of kernels_eq.cu, everything on the handle's main stream.
+extern "C" dtl_status dtl_b200_equalize_noalloc(dtl_b200* h, const float* freq, const float* taps, const dtl_frame_meta* meta,
+                                                int32_t n_streams, int32_t frames_per_stream,
+                                                dtl_frame_result* res, float* llr, int32_t* n_llr)
+{
+    if (!h || !freq || !taps || !meta || !res || n_streams < 0 || frames_per_stream < 0) return DTL_ERR_INVALID_ARG;
+    CK(cudaSetDevice(h->device));
+    if (h->n_streams != n_streams)
+        return fail(h, DTL_ERR_INVALID_ARG, "dtl_b200_equalize_noalloc: per-stream state is sized for " + std::to_string(h->n_streams) +
+                    " streams, the call has " + std::to_string(n_streams) + ": call dtl_b200_reset(n_streams) first (this entry point does not allocate)");
+    const long long n = (long long)n_streams * frames_per_stream;
+    if (n == 0) return DTL_OK;
+    cudaError_t je = side_join(h);                  // whatever an earlier call left on the side stream is ordered in front
+    if (je != cudaSuccess) return cuda_fail(h, je, "side stream join");
+    if (h->hdr_pending) { h->hdr_pending = false; CK(cudaStreamWaitEvent(h->stream, h->ev_hdr, 0)); }
+    EqParams p;
+    memset(&p, 0, sizeof p);
+    p.pl = h->pl; p.cn = h->cn; p.freq = (const float2*)freq; p.taps = (const float2*)taps; p.meta = meta; p.n_frames = n;
+    p.res = res; p.llr = llr; p.llr_stride = h->llr_stride; p.n_llr = n_llr; p.sgn_stride = h->sgn_stride;
+    p.bytes_stride = h->bytes_stride; p.crc_table = h->crc_table; p.err = h->d_err; p.tw = h->tw;
+    int why = 0;
+    long long need = 0, have = 0;
+    CK(launch_eq_noalloc(h->stream, p, &why, &need, &have));
+    if (why == 1) return fail(h, DTL_ERR_UNSUPPORTED, "dtl_b200_equalize_noalloc: this carrier plan needs the general equaliser kernel (use dtl_b200_equalize)");
+    if (why == 2)
+        return fail(h, DTL_ERR_CAPACITY, "dtl_b200_equalize_noalloc: " + std::to_string(n) + " frames x " + std::to_string(std::max(h->pl.npil_frame, 1)) +
+                    " pilots = " + std::to_string(need) + " floats of scratch, the static array holds " + std::to_string(have) +
+                    " (DTL_B200_NOALLOC_MAX_PILOT_FLOATS): split the call or use dtl_b200_equalize");
+    if (why == 3) return fail(h, DTL_ERR_CUDA, "dtl_b200_equalize_noalloc: static scratch not set up on this device");
+    StreamParams sp;
+    sp.st = (StreamState*)h->st_buf.p + h->s_off; sp.n_streams = n_streams; sp.F = frames_per_stream; sp.meta = meta; sp.res = res;
+    sp.n_mcs = h->n_mcs; sp.mcs_snr = h->d_mcs_snr; sp.mcs_cnst = h->d_mcs_cnst; sp.mcs_fec = h->d_mcs_fec;
+    sp.hysteresis = h->hysteresis; sp.decision_th = h->decision_th;
+    CK(launch_stream_state(h->stream, sp));
+    h->launches += 3;
+    return DTL_OK;
+}
+
 // ---- stage 3 / 5a stand-alone blocks -------------------------------------------------------------------------------------------------
 static dtl_status demap_common(dtl_b200* h, int mode, const float* syms, const uint8_t* in_chunks, int32_t stride_syms,
                                const dtl_frame_meta* meta, const double* noise, int64_t n_frames, float* llr, int32_t llr_stride,

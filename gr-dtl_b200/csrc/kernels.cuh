@@ -190,6 +190,8 @@ cudaError_t launch_eq(cudaStream_t st, const EqParams& p, int* launches = nullpt
 // tags_deferred != nullptr: the lean kernel's snr_tags_kernel is left to the caller (launch_snr_tags, any stream ordered
 // after `st`), *tags_deferred says whether one is due
 cudaError_t launch_snr_tags(cudaStream_t st, const EqParams& p);
+// eq_fast_kernel + snr_tags_kernel with p.mag replaced by the library's static device scratch (no allocation; kernels_eq.cu)
+cudaError_t launch_eq_noalloc(cudaStream_t st, const EqParams& p, int* why, long long* need, long long* have);
 // sign words of n_frames rows of llr_stride floats: sgn[f][w] bit b = llr[f][32 w + b] > 0 (rows padded with zeros to sgn_stride words)
 cudaError_t launch_llr_sign(cudaStream_t st, const float* llr, int llr_stride, long long n_frames, uint32_t* sgn, int sgn_stride);
 cudaError_t launch_stream_reset(cudaStream_t st, StreamState* state, int n, int initial_mcs);

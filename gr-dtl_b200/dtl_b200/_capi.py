@@ -53,7 +53,7 @@ SYMBOLS = (
     "dtl_b200_sync", "dtl_b200_cuda_stream", "dtl_b200_frame_capacity", "dtl_b200_frame_samples",
     "dtl_b200_llr_stride", "dtl_b200_bytes_stride", "dtl_b200_code_info", "dtl_b200_launch_count",
     "dtl_b200_profile", "dtl_b200_stage_times",
-    "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize",
+    "dtl_b200_host_alloc", "dtl_b200_host_free", "dtl_b200_demod", "dtl_b200_fft", "dtl_b200_equalize", "dtl_b200_equalize_noalloc",
     "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode",
     "dtl_b200_rx", "dtl_b200_tx", "dtl_b200_rx_headers", "dtl_b200_rx_iq", "dtl_b200_fec_frame", "dtl_b200_rx_stream")
 
@@ -99,6 +99,7 @@ def lib():
         L.dtl_b200_demod.argtypes = [vp, vp, i64, vp, C.c_int]
         L.dtl_b200_fft.argtypes = [vp, vp, i64, C.c_int, vp, C.c_int]
         L.dtl_b200_equalize.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int]
+        L.dtl_b200_equalize_noalloc.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, vp]
         L.dtl_b200_soft_demap.argtypes = [vp, vp, i32, vp, vp, i64, vp, i32, C.c_int]
         L.dtl_b200_hard_demap.argtypes = [vp, vp, i32, vp, i64, vp, C.c_int]
         L.dtl_b200_map.argtypes = [vp, vp, i32, vp, i64, vp, C.c_int]

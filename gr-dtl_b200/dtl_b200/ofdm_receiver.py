@@ -268,6 +268,18 @@ class ofdm_receiver:
                                              g("res"), g("llr"), g("n_llr"), g("bytes"), g("nbytes"), g("crc_ok"), mem))
         return o
 
+    def equalize_noalloc(self, freq, taps, meta, n_streams, frames_per_stream, out):
+        """dtl_b200_equalize_noalloc: the lean equaliser pass for callers that must not allocate.  Device tensors only, and
+        `out` must carry the preallocated device buffers res [S*F] (+ optionally llr [S*F, llr_stride], n_llr [S*F]); nothing
+        is allocated here or in the library.  Call reset(n_streams) first; sync() before reading."""
+        a_f, a_t, a_m = _Arg(freq), _Arg(taps), _Arg(meta)
+        if _mem_of(a_f, a_t, a_m) != MEM_DEVICE or "res" not in out or any(not _is_torch(v) for v in out.values()):
+            raise ValueError("equalize_noalloc takes device buffers only, and a preallocated out['res']")
+        g = lambda k: _Arg(out.get(k)).ptr
+        self._ck(self._lib.dtl_b200_equalize_noalloc(self._h, a_f.ptr, a_t.ptr, a_m.ptr, int(n_streams), int(frames_per_stream),
+                                                     g("res"), g("llr"), g("n_llr")))
+        return out
+
     # ---- stand-alone blocks ---------------------------------------------------------------------------------
     def soft_demap(self, syms, meta, noise=None):
         """dtl.ofdm_adaptive_constellation_soft_cf(constellations, len_key): syms [n_frames, stride]"""

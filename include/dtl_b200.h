@@ -189,6 +189,26 @@ dtl_status dtl_b200_equalize(dtl_b200* h, const float* freq, const float* taps, 
                              float* out_hard, float* out_soft, float* taps_out, dtl_frame_result* res,
                              float* llr, int32_t* n_llr, uint8_t* bytes, int32_t* nbytes, int32_t* crc_ok, int mem);
 
+/* ---- the equaliser pass without any allocation ----------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and the same kernels as
+ * dtl_b200_equalize for the FEC chain's outputs -- res (tags + feedback), llr / n_llr (nullable) -- but
+ *   * every pointer is a DEVICE pointer of the handle's device; the call only enqueues on the handle's stream
+ *     (dtl_b200_sync before reading) and calls no cudaMalloc / cudaFree or allocating library routine;
+ *   * the per-frame scratch (|equalised pilot| magnitudes between the equaliser pass and the SNR-tag pass) is a static device
+ *     array inside the library: DTL_B200_NOALLOC_MAX_PILOT_FLOATS floats = 2 MiB that every GPU which loads libdtl_b200.so holds
+ *     until exit.  n_streams * frames_per_stream * (pilot carriers per frame) beyond it -> DTL_ERR_CAPACITY
+ *     (64-carrier PHY, 20 symbols: 80 pilots per frame = 6553 frames per call);
+ *   * per-stream state must already be sized: dtl_b200_reset(h, n_streams) before the first call, else DTL_ERR_INVALID_ARG;
+ *     carrier plans the lean kernel does not cover -> DTL_ERR_UNSUPPORTED.
+ * All calls on one device share the scratch array, which keeps the last call's contents; every slice that is read is written
+ * first by the same call, so nothing carries over -- but calls that OVERLAP on the GPU (two handles / streams of one device)
+ * race on it: serialise them. */
+#define DTL_B200_NOALLOC_MAX_PILOT_FLOATS 524288
+dtl_status dtl_b200_equalize_noalloc(dtl_b200* h, const float* freq, const float* taps, const dtl_frame_meta* meta,
+                                     int32_t n_streams, int32_t frames_per_stream,
+                                     dtl_frame_result* res, float* llr, int32_t* n_llr);
+
 /* ---- stage 3 stand-alone blocks -----------------------------------------------------------------------------
  * ofdm_adaptive_constellation_soft_cf: syms c64 [n_frames][stride_syms], per frame meta.constellation,
  * meta.packet_len symbols, noise[n_frames] = "noise_tag_key" (NULL or <0 entry: sigma = 0.001, :89);
