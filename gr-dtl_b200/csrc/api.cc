@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <random>
 #include <mutex>
 
 using namespace dtl;
@@ -149,27 +150,169 @@ double sigma2_for_lr(double s2)
 }
 
 // Steps of the layered decoder (bp_layered.cuh): groups of check rows that share no variable, at most 32 rows each, one lane
-// per row.  Greedy colouring: rows in order, each into the first group that holds none of its variables and has a free
-// lane (13 groups for the n = 300 code).  Packing the rows into ceil(m / 32) full groups and resolving the few shared
-// variables with shared-memory atomic adds was measured slower (float atomics on shared memory are compare-and-swap loops).
+// per row.  A step costs the same whether 5 or 32 of its lanes work, so the colouring is BALANCED: the smallest number of groups
+// K >= ceil(m / 32) for which a randomised most-constrained-first colouring with capacity 32 succeeds (5 groups for the 148
+// rows of the n = 300 code; first-fit in row order gave 13).  Fixed seed: the schedule is the same in every process.
 std::vector<std::vector<int>> schedule_rows(const std::vector<std::vector<int>>& mlist, int n, int* shared_out)
 {
-    std::vector<std::vector<int>> groups;
-    std::vector<std::vector<char>> used;
-    for (int r = 0; r < (int)mlist.size(); r++) {
-        int g = -1;
-        for (size_t k = 0; k < groups.size() && g < 0; k++) {
-            if (groups[k].size() >= 32) continue;
-            bool ok = true;
-            for (int v : mlist[r]) if (used[k][v]) { ok = false; break; }
-            if (ok) g = (int)k;
-        }
-        if (g < 0) { groups.emplace_back(); used.emplace_back(n, 0); g = (int)groups.size() - 1; }
-        groups[g].push_back(r);
-        for (int v : mlist[r]) used[g][v] = 1;
-    }
+    const int m = (int)mlist.size();
     if (shared_out) *shared_out = 0;
-    return groups;
+    std::vector<std::vector<int>> rows_of(n);
+    for (int r = 0; r < m; r++) for (int v : mlist[r]) rows_of[v].push_back(r);
+    std::vector<std::vector<int>> adj(m);
+    for (int r = 0; r < m; r++) {
+        for (int v : mlist[r]) for (int r2 : rows_of[v]) if (r2 != r) adj[r].push_back(r2);
+        std::sort(adj[r].begin(), adj[r].end());
+        adj[r].erase(std::unique(adj[r].begin(), adj[r].end()), adj[r].end());
+    }
+    std::mt19937 rng(0x1A7E12u);
+    for (int K = std::max(1, (m + 31) / 32); K <= m; K++) {
+        for (int trial = 0; trial < 600; trial++) {
+            std::vector<int> colour(m, -1), size(K, 0);
+            std::vector<std::vector<char>> banned(m, std::vector<char>(K, 0));
+            bool ok = true;
+            for (int done = 0; done < m && ok; done++) {
+                // the uncoloured row with the fewest feasible groups (ties: random)
+                int best = -1, best_feas = K + 1, ties = 0;
+                for (int r = 0; r < m; r++) {
+                    if (colour[r] >= 0) continue;
+                    int feas = 0;
+                    for (int k = 0; k < K; k++) feas += !banned[r][k] && size[k] < 32;
+                    if (feas < best_feas) { best = r; best_feas = feas; ties = 1; }
+                    else if (feas == best_feas && (int)(rng() % (unsigned)++ties) == 0) best = r;
+                }
+                if (best_feas == 0) { ok = false; break; }
+                // into the feasible group with the fewest rows (keeps the groups level), ties random
+                int g = -1, gs = 33, gt = 0;
+                for (int k = 0; k < K; k++) {
+                    if (banned[best][k] || size[k] >= 32) continue;
+                    if (size[k] < gs) { g = k; gs = size[k]; gt = 1; }
+                    else if (size[k] == gs && (int)(rng() % (unsigned)++gt) == 0) g = k;
+                }
+                colour[best] = g; size[g]++;
+                for (int r2 : adj[best]) banned[r2][g] = 1;
+            }
+            if (!ok) continue;
+            std::vector<std::vector<int>> groups(K);
+            for (int r = 0; r < m; r++) groups[colour[r]].push_back(r);
+            groups.erase(std::remove_if(groups.begin(), groups.end(), [](const std::vector<int>& g) { return g.empty(); }), groups.end());
+            return groups;
+        }
+    }
+    std::vector<std::vector<int>> single;                       // unreachable (K = m always succeeds)
+    for (int r = 0; r < m; r++) single.push_back({ r });
+    return single;
+}
+
+// Placement of the layered decoder's posteriors (bp_layered.cuh).  Every variable gets a slot (bank = slot % 32) such that, per
+// step, a bank holds at most `rmax` of the step's variables wherever the graph allows (greedy start + hill climbing on the
+// overflow count); each step's rows then order their edges by a bipartite edge colouring rows x banks with rmax colours, so the
+// j-th access of the step's lanes goes to distinct banks (Koenig: always possible without overflow).  Returns the slot of every
+// variable, the slot count ns, per row the variable at each edge position (-1 = pad) and the wavefronts beyond one per access
+// that are left (0 = conflict-free).
+struct LayPlacement { std::vector<int> slot; int ns = 0; std::vector<std::vector<int>> row_edges; int extra = 0; };
+LayPlacement lay_assign_slots(const std::vector<std::vector<int>>& groups, const std::vector<std::vector<int>>& mlist, int n, int rmax)
+{
+    const int NB = 32, S = (int)groups.size();
+    LayPlacement out;
+    out.ns = ((n + NB - 1) / NB + 1) * NB;
+    const int cap = out.ns / NB;
+    std::vector<std::vector<int>> steps_of(n);
+    for (int s = 0; s < S; s++) for (int r : groups[s]) for (int v : mlist[r]) steps_of[v].push_back(s);
+    std::mt19937 rng(0xB4A2C5u);
+    std::vector<int> bank(n, -1), fill(NB, 0);
+    std::vector<std::vector<int>> cnt(S, std::vector<int>(NB, 0));
+    std::vector<int> order(n);
+    for (int v = 0; v < n; v++) order[v] = v;
+    std::shuffle(order.begin(), order.end(), rng);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return steps_of[a].size() > steps_of[b].size(); });
+    for (int v : order) {
+        int best = -1, bc = 1 << 30, ties = 0;
+        for (int b = 0; b < NB; b++) {
+            if (fill[b] >= cap) continue;
+            int c = 0;
+            for (int s : steps_of[v]) c += cnt[s][b] * 16 + (cnt[s][b] >= rmax ? 1000 : 0);
+            c += fill[b];
+            if (c < bc) { best = b; bc = c; ties = 1; }
+            else if (c == bc && (int)(rng() % (unsigned)++ties) == 0) best = b;
+        }
+        bank[v] = best; fill[best]++;
+        for (int s : steps_of[v]) cnt[s][best]++;
+    }
+    auto overflow_of = [&](int v, int b) { int o = 0; for (int s : steps_of[v]) o += cnt[s][b] > rmax; return o; };   // v counted in cnt
+    for (int it = 0; it < 200000; it++) {
+        // a variable that sits in an overfull (step, bank) moves to the bank where it overflows least (or swaps with one there)
+        int total = 0;
+        for (int s = 0; s < S; s++) for (int b = 0; b < NB; b++) total += std::max(0, cnt[s][b] - rmax);
+        if (!total) break;
+        const int v = (int)(rng() % (unsigned)n);
+        if (!overflow_of(v, bank[v])) continue;
+        const int b0 = bank[v], b1 = (int)(rng() % (unsigned)NB);
+        if (b1 == b0) continue;
+        auto move = [&](int x, int from, int to) { for (int s : steps_of[x]) { cnt[s][from]--; cnt[s][to]++; } bank[x] = to; fill[from]--; fill[to]++; };
+        int u = -1;
+        if (fill[b1] >= cap) {                                  // full: swap with a random variable of b1
+            std::vector<int> cand;
+            for (int x = 0; x < n; x++) if (bank[x] == b1) cand.push_back(x);
+            u = cand[rng() % cand.size()];
+        }
+        move(v, b0, b1);
+        if (u >= 0) move(u, b1, b0);
+        int after = 0;
+        for (int s = 0; s < S; s++) for (int b = 0; b < NB; b++) after += std::max(0, cnt[s][b] - rmax);
+        if (after > total) { if (u >= 0) move(u, b0, b1); move(v, b1, b0); }
+    }
+    out.slot.assign(n, 0);
+    std::vector<int> next(NB, 0);
+    for (int v = 0; v < n; v++) out.slot[v] = bank[v] + NB * next[bank[v]]++;
+    // edge order per step: bipartite edge colouring (rows of the step x banks) with rmax colours, alternating-path recolouring
+    out.row_edges.assign(mlist.size(), std::vector<int>(rmax, -1));
+    for (int s = 0; s < S; s++) {
+        const int R = (int)groups[s].size();
+        std::vector<int> eu, eb, ev, ecol;
+        for (int l = 0; l < R; l++) for (int v : mlist[groups[s][l]]) { eu.push_back(l); eb.push_back(bank[v]); ev.push_back(v); ecol.push_back(-1); }
+        std::vector<std::vector<int>> colU(R, std::vector<int>(rmax, -1)), colB(NB, std::vector<int>(rmax, -1));
+        for (int e = 0; e < (int)eu.size(); e++) {
+            int cu = -1, cb = -1;
+            for (int c = 0; c < rmax && cu < 0; c++) if (colU[eu[e]][c] < 0) cu = c;
+            for (int c = 0; c < rmax && cb < 0; c++) if (colB[eb[e]][c] < 0) cb = c;
+            if (cu < 0) continue;                               // row heavier than rmax: cannot happen (rmax = max row weight)
+            if (cb >= 0 && colB[eb[e]][cu] >= 0 && cb != cu) {  // free cu at the bank: flip the cu/cb path that starts there
+                std::vector<int> path;
+                int node = eb[e], col = cu;
+                bool at_bank = true;
+                while (path.size() < eu.size()) {
+                    const int e2 = at_bank ? colB[node][col] : colU[node][col];
+                    if (e2 < 0) break;
+                    path.push_back(e2);
+                    node = at_bank ? eu[e2] : eb[e2];
+                    at_bank = !at_bank;
+                    col = col == cu ? cb : cu;
+                }
+                for (int e2 : path) { colU[eu[e2]][ecol[e2]] = -1; if (colB[eb[e2]][ecol[e2]] == e2) colB[eb[e2]][ecol[e2]] = -1; }
+                for (int e2 : path) { ecol[e2] = ecol[e2] == cu ? cb : cu; colU[eu[e2]][ecol[e2]] = e2; colB[eb[e2]][ecol[e2]] = e2; }
+            }
+            ecol[e] = cu; colU[eu[e]][cu] = e; colB[eb[e]][cu] = e;
+        }
+        bool valid = true;
+        for (int l = 0; l < R && valid; l++) {
+            std::vector<int> seen(rmax, 0);
+            int have = 0;
+            for (int e = 0; e < (int)eu.size(); e++) if (eu[e] == l) { if (ecol[e] < 0 || seen[ecol[e]]++) valid = false; have++; }
+            if (have != (int)mlist[groups[s][l]].size()) valid = false;
+        }
+        for (int l = 0; l < R; l++) {
+            auto& re = out.row_edges[groups[s][l]];
+            if (valid) { for (int e = 0; e < (int)eu.size(); e++) if (eu[e] == l) re[ecol[e]] = ev[e]; }
+            else for (size_t j = 0; j < mlist[groups[s][l]].size(); j++) re[j] = mlist[groups[s][l]][j];
+        }
+        for (int j = 0; j < rmax; j++) {
+            int c[32] = { 0 }, mx = 1;
+            for (int l = 0; l < R; l++) { const int v = out.row_edges[groups[s][l]][j]; if (v >= 0) mx = std::max(mx, ++c[bank[v]]); }
+            out.extra += mx - 1;
+        }
+    }
+    return out;
 }
 
 // Assignment of the variables to (round, lane) positions of the decoder's column pass (bp_ref.cuh: var_pass).  The pass is
@@ -588,22 +731,30 @@ static dtl_status build_tables(dtl_b200* h, const dtl_config* c)
             d.fast = bp_ref_has_instance(code.max_row, code.max_col) && dummy + 1 <= 65535 && code.n + 2 <= 65535;
             const bool have_rv2 = code.max_row <= 7 && dummy + 1 <= 65535 && code.n + 2 <= 65535;
             if (have_rv2) {                      // layered decoder: row groups (bp_layered.cuh)
-                const auto groups = schedule_rows(code.mlist, code.n, &code.lay_shared);
-                // one 16-byte descriptor per (step, lane): the row's variables (pad: n) and the row id (0xffff = idle lane)
-                std::vector<uint16_t> lrows(groups.size() * 32 * 8, (uint16_t)code.n);
+                const auto groups = schedule_rows(code.mlist, code.n, nullptr);
+                const int rmx = std::max(code.max_row, 1);
+                const LayPlacement pl_ = lay_assign_slots(groups, code.mlist, code.n, rmx);
+                code.lay_shared = pl_.extra;                      // wavefronts beyond one per access the placement leaves
+                if (getenv("DTL_LAY_DEBUG"))
+                    fprintf(stderr, "layered schedule n=%d m=%d: %zu steps, %d slots, %d extra wavefronts per iteration\n", code.n, code.m, groups.size(), pl_.ns, pl_.extra);
+                // one 16-byte descriptor per (step, lane): the slots of the row's variables (pad: ns) and the row id (0xffff = idle lane)
+                std::vector<uint16_t> lrows(groups.size() * 32 * 8, (uint16_t)pl_.ns);
                 for (size_t g = 0; g < groups.size(); g++)
                     for (size_t l = 0; l < 32; l++) {
                         uint16_t* ds = &lrows[(g * 32 + l) * 8];
                         ds[7] = 0xffff;
                         if (l < groups[g].size()) {
                             const int r = groups[g][l];
-                            for (size_t j = 0; j < code.mlist[r].size() && j < 7; j++) ds[j] = (uint16_t)code.mlist[r][j];
+                            for (int j = 0; j < rmx && j < 7; j++) if (pl_.row_edges[r][j] >= 0) ds[j] = (uint16_t)pl_.slot[pl_.row_edges[r][j]];
                             ds[7] = (uint16_t)r;
                         }
                     }
+                std::vector<uint16_t> lperm(code.n);
+                for (int q = 0; q < code.n; q++) lperm[q] = (uint16_t)pl_.slot[perm[q]];
                 d.lay_steps = (int)groups.size(); d.lay_rows = h->upload(lrows, e);
+                d.lay_ns = pl_.ns; d.lay_perm = h->upload(lperm, e);
                 h->lay_tab_bytes += (int)lay_tab_bytes(code.n, code.m, d.lay_steps);
-                h->lay_warp_bytes = std::max(h->lay_warp_bytes, (int)lay_warp_bytes(code.n, code.m, rs));
+                h->lay_warp_bytes = std::max(h->lay_warp_bytes, (int)lay_warp_bytes(d.lay_ns, d.lay_steps));
             } else h->all_lay = false;
             if (have_rv2 && !d.fast) {           // the layered decoder needs the row table even where the reference one has no instance
                 std::vector<uint16_t> rv2l((size_t)code.m * 8, (uint16_t)code.n);
@@ -1233,7 +1384,7 @@ extern "C" dtl_status dtl_b200_ldpc_decode(dtl_b200* h, int32_t fec_id, const fl
     p.fast_tab_bytes = (int)fast_tab_bytes(c.n, c.m, c.dev.nvr); p.fast_warp_bytes = (int)fast_warp_bytes(c.n, c.m, c.dev.rs);
     p.exp_tab = h->d_exp_tab; p.sigma2_lr = sigma2_for_lr(h->sigma2);
     p.lay = h->ldpc_mode == DTL_LDPC_LAYERED && c.dev.lay_steps > 0 && !h->no_fast_bp;
-    p.lay_tab_bytes = (int)lay_tab_bytes(c.n, c.m, c.dev.lay_steps); p.lay_warp_bytes = (int)lay_warp_bytes(c.n, c.m, c.dev.rs);
+    p.lay_tab_bytes = (int)lay_tab_bytes(c.n, c.m, c.dev.lay_steps); p.lay_warp_bytes = (int)lay_warp_bytes(c.dev.lay_ns, c.dev.lay_steps);
     p.llr = sg.in(SL_LLR, llr, (size_t)count * c.n);
     p.bits = sg.out(SL_BITS_OUT, bits, (size_t)count * c.k);
     p.nit = sg.out(SL_NIT, nit, (size_t)count);

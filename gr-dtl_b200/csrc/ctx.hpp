@@ -91,7 +91,9 @@ struct CodeDev {
     int nvr;                     // variable rounds: ceil(n / 32)
     const uint4* rv2;            // [m] variables of the row's edges as 8 x u16 in mlist order (pad: n)
     int lay_steps;               // layered decoder (bp_layered.cuh): groups of variable-disjoint rows, one step each
-    const uint16_t* lay_rows;    // [lay_steps][32][8] per (step, lane): the row's variables (pad: n), [7] = row id (0xffff = idle)
+    const uint16_t* lay_rows;    // [lay_steps][32][8] per (step, lane): the row's variable SLOTS (pad: lay_ns), [7] = row id (0xffff = idle)
+    int lay_ns;                  // posterior slots (>= n; bank-conflict-aware placement of the variables, api.cc: lay_assign_slots)
+    const uint16_t* lay_perm;    // [n] wire position -> slot
     const uint4* vdesc;          // [nvr*32] one entry per (round, lane): x = slot0 | slot1 << 16, y = slot2 | slot3 << 16 in nlist
                                  //   order (pad: the dummy slot m*rs, which holds 1.0), z = variable (idle lane: n + 1)
 };

@@ -28,11 +28,12 @@ __host__ __device__ inline size_t fast_warp_bytes(int n, int m, int rs)
 // layered decoder (bp_layered.cuh)
 __host__ __device__ inline size_t lay_tab_bytes(int n, int m, int steps)
 {
-    return 16 * (size_t)m + 512 * (size_t)steps + ((2 * (size_t)n + 15) & ~(size_t)15);
+    (void)m;
+    return 512 * (size_t)steps + ((2 * (size_t)n + 15) & ~(size_t)15);      // row descriptors + wire position -> slot
 }
-__host__ __device__ inline size_t lay_warp_bytes(int n, int m, int rs)
+__host__ __device__ inline size_t lay_warp_bytes(int ns, int steps)
 {
-    return (((size_t)m * rs * 4 + 15) & ~(size_t)15) + ((((size_t)n + 2) * 4 + 15) & ~(size_t)15) + (((size_t)n + 2 + 15) & ~(size_t)15);
+    return (((size_t)steps * 32 * 3 * 4 + 15) & ~(size_t)15) + ((((size_t)ns + 1) * 4 + 15) & ~(size_t)15);   // compressed messages + posteriors by slot
 }
 inline bool bp_ref_has_instance(int max_row, int max_col)
 {
