@@ -581,6 +581,43 @@ def run_b200(a):
                           "headers instead of the caller"}
         del out2
 
+    # ---- continuous IQ: the synchroniser in front of everything.  The batch's frames of a stream lie back to
+    # back in memory, so [S, F * frame_samples] IS a continuous stream; every call feeds the next F frames' worth of samples
+    # (the same samples again: the stream goes on) and gets the frames that were completed by them.
+    from_stream = None
+    if not a.no_from_iq:
+        Fc = F + 2
+        out3 = new_out(rx, S, Fc, dev_alloc, np)
+        out3["meta"] = rx._new(dtl_b200.MEM_DEVICE, (S * Fc,), dtl_b200.frame_meta_dtype)
+        out3["hres"] = rx._new(dtl_b200.MEM_DEVICE, (S * Fc,), dtl_b200.header_result_dtype)
+        out3["n_frames"] = rx._new(dtl_b200.MEM_DEVICE, (S,), np.int32)
+        out3["frame_start"] = rx._new(dtl_b200.MEM_DEVICE, (S * Fc,), np.int64)
+        rx.reset(S)
+
+        def step_stream():
+            rx.rx_stream(iq, S, Fc, out=out3)
+
+        for _ in range(3):
+            step_stream()
+        rx.sync()
+        nfr = out3["n_frames"].cpu().numpy()
+        hdr3 = out3["hres"].cpu().numpy().view(dtl_b200.header_result_dtype)["crc_ok"].reshape(S, Fc)
+        ms_st = ctx.timed(rx, step_stream, min(a.steps, 20))
+        rx.stage_times(reset=True)
+        rx.profile(True)
+        for _ in range(3):
+            step_stream()
+        rx.sync()
+        sync_ms = rx.stage_times(reset=True)["sync"][0] / 3
+        rx.profile(False)
+        from_stream = {"value": samples_all / (ms_st * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_st,
+                       "sync_front_end_ms_per_step": sync_ms, "frames_found_per_call": int(nfr.sum()), "frames_sent_per_call": S * F,
+                       "headers_parsed_per_call": int(hdr3.sum()),
+                       "api": "dtl_b200_rx_stream(mem=DTL_MEM_DEVICE): continuous IQ; Schmidl & Cox timing + fine CFO, trigger "
+                              "regulariser, frame cut, then the path from IQ alone"}
+        del out3
+        rx.reset(S)
+
     # ---- TX FEC framer: user bytes -> chunks + tags for the same S x F frames, device-resident
     tx_framer = None
     if not a.no_from_iq:
@@ -713,7 +750,7 @@ def run_b200(a):
         "data": "synthetic", "decoded_mbit_per_s": bits_all / (ms_step * 1e-3) / 1e6,
         "config": config_dict(a, S),
         "verified": {"tbs_per_step_per_gpu": n_tbs, "crc_ok_tbs": int(ok_ref.sum()), "check": "decoded bytes == transmitted payload"},
-        "e2e": e2e, "e2e_from_iq": e2e_iq, "sustained": sustained, "rx_from_iq": from_iq, "tx_fec_framer": tx_framer,
+        "e2e": e2e, "e2e_from_iq": e2e_iq, "sustained": sustained, "rx_from_iq": from_iq, "rx_from_stream": from_stream, "tx_fec_framer": tx_framer,
         "h2d_ceiling": ceiling, "numa": ctx.numa,
         "gpu_launches": int(launches), "ms_per_step_serial": ms_serial, "clocks": clocks,
         "roofline": roofline, "roofline_ldpc": roofline_ldpc, "stages": stage_tab,

@@ -374,7 +374,7 @@ class ofdm_receiver:
                                           g("nbytes"), g("tbs"), tb_cap, g("ntbs"), g("frame_crc"), mem))
         return o
 
-    def rx_stream(self, iq, n_streams, frames_cap, bytes_cap=None, tb_cap=None, want_frames=False):
+    def rx_stream(self, iq, n_streams, frames_cap, bytes_cap=None, tb_cap=None, want_frames=False, out=None):
         """The receive path from CONTINUOUS IQ (python/dtl/ofdm_receiver.py:70-97 in front of the header and payload branches):
         Schmidl & Cox synchroniser, fine-CFO mixer, trigger regulariser, then rx_iq on the frames found.  iq: [S, T] the next T
         samples of every stream (state is kept between calls).  Returns the rx_iq outputs for S x frames_cap frame slots plus
@@ -384,15 +384,20 @@ class ofdm_receiver:
         a = _Arg(iq)
         mem = a.mem
         T = (iq.numel() if _is_torch(iq) else iq.size) // S
-        bytes_cap = bytes_cap or (self.bytes_stride + 8) * (F + 1)
-        tb_cap = tb_cap or 2 * F + 1
-        o = dict(res=self._new(mem, (S * F,), frame_result_dtype), bytes=self._new(mem, (S, bytes_cap), np.uint8),
-                 nbytes=self._new(mem, (S,), np.int32), tbs=self._new(mem, (S, tb_cap), tb_result_dtype),
-                 ntbs=self._new(mem, (S,), np.int32), frame_crc=self._new(mem, (S * F,), np.int32),
-                 meta=self._new(mem, (S * F,), frame_meta_dtype), hres=self._new(mem, (S * F,), header_result_dtype),
-                 n_frames=self._new(mem, (S,), np.int32), frame_start=self._new(mem, (S * F,), np.int64))
-        if want_frames:
-            o["frames"] = self._new(mem, (S * F, self.frame_samples), np.complex64)
+        if out is not None:                                # preallocated buffers (same keys): no allocation in a timed loop
+            o = out
+            bytes_cap = o["bytes"].shape[1]
+            tb_cap = o["tbs"].shape[1] if not _is_torch(o["tbs"]) else o["tbs"].numel() // (S * tb_result_dtype.itemsize)
+        else:
+            bytes_cap = bytes_cap or (self.bytes_stride + 8) * (F + 1)
+            tb_cap = tb_cap or 2 * F + 1
+            o = dict(res=self._new(mem, (S * F,), frame_result_dtype), bytes=self._new(mem, (S, bytes_cap), np.uint8),
+                     nbytes=self._new(mem, (S,), np.int32), tbs=self._new(mem, (S, tb_cap), tb_result_dtype),
+                     ntbs=self._new(mem, (S,), np.int32), frame_crc=self._new(mem, (S * F,), np.int32),
+                     meta=self._new(mem, (S * F,), frame_meta_dtype), hres=self._new(mem, (S * F,), header_result_dtype),
+                     n_frames=self._new(mem, (S,), np.int32), frame_start=self._new(mem, (S * F,), np.int64))
+            if want_frames:
+                o["frames"] = self._new(mem, (S * F, self.frame_samples), np.complex64)
         g = lambda k: _Arg(o.get(k)).ptr
         self._ck(self._lib.dtl_b200_rx_stream(self._h, a.ptr, S, T, F, g("n_frames"), g("frame_start"), g("frames"), g("meta"),
                                               g("hres"), g("res"), g("bytes"), bytes_cap, g("nbytes"), g("tbs"), tb_cap,

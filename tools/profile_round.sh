@@ -27,11 +27,12 @@ python tools/leg.py config1 4 3 > $O/${tag}_leg_config1.json 2>> $O/${tag}_bench
 ncu --set full --clock-control none -o $O/${tag}_c1 -f -k regex:"eq_fast|tb_|frame_gather|fft64" -c 8 python tools/leg.py config1 4 2 > $O/${tag}_ncu4.log 2>&1
 python tools/ncu_metrics.py $O/${tag}_c1.ncu-rep $O/${tag}_ncu_config1_metrics.csv > $O/${tag}_ncu_config1_metrics.txt 2>&1
 python tools/leg.py config5 6 3 > $O/${tag}_leg_config5.json 2>> $O/${tag}_bench.err && \
-ncu --set full --clock-control none -o $O/${tag}_c5 -f -k regex:"eq_fast|fft_fwd|ldpc_screen|tb_finish" -c 8 python tools/leg.py config5 6 2 > $O/${tag}_ncu5.log 2>&1
+ncu --set full --clock-control none -o $O/${tag}_c5 -f -k regex:"eq_fast|fft1024|fft_fwd|ldpc_screen|tb_finish|tb_gather" -c 10 python tools/leg.py config5 6 2 > $O/${tag}_ncu5.log 2>&1
 python tools/ncu_metrics.py $O/${tag}_c5.ncu-rep $O/${tag}_ncu_config5_metrics.csv > $O/${tag}_ncu_config5_metrics.txt 2>&1
 for c in 1 2 3 5 6; do
   ncu --set full --clock-control none -o $O/${tag}_c3_$c -f -k regex:"eq_fast" -c 1 --launch-skip 2 python tools/leg.py config3 $c 2 > $O/${tag}_ncu6_$c.log 2>&1
   python tools/ncu_metrics.py $O/${tag}_c3_$c.ncu-rep $O/${tag}_ncu_config3_cnst$c.csv > $O/${tag}_ncu_config3_cnst$c.txt 2>&1
 done
-rm -f $O/${tag}_c3_*.ncu-rep $O/${tag}_c1.ncu-rep $O/${tag}_c5.ncu-rep
+rm -f $O/${tag}_c3_*.ncu-rep $O/${tag}_c1.ncu-rep $O/${tag}_c5.ncu-rep $O/${tag}_main.ncu-rep $O/${tag}_lay.ncu-rep
+python bench.py --impl reference --steps 3 --warmup 1 > $O/${tag}_bench_reference_arm.json 2>> $O/${tag}_bench.err
 ls -la $O | grep ${tag} | head -40
