@@ -54,41 +54,51 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
     const long long total = st.total + p.T;
     if (p0 >= total) return;
     const float2* w = p.w_new + (size_t)s * p.w_cap;
+    // The scan arrays are padded by one element per 32 (PAD): the per-block chains below start 32 or 64 elements apart, which
+    // without the padding is ONE bank for every thread of the warp (a 32-way conflict on every access).
+#define PAD(i) ((i) + ((i) >> 5))
     float2* xs = (float2*)sm;                                   // x[p0 - N - W1 .. p0 + TILE)
-    float2* cs = xs + (TILE + N + W1);                          // c[p0 - N .. p0 + TILE)
-    float2* pc = cs + (TILE + N);
-    float2* sc = pc + (TILE + N);
-    float* es = (float*)(sc + (TILE + N));
-    float* pe = es + (TILE + N);
-    float* se = pe + (TILE + N);
-    const int nx = TILE + N + W1, nc = TILE + N;
+    const int nx = TILE + N + W1, nc = TILE + N, ncp = PAD(nc) + 1;
+    float2* cs = xs + nx;                                       // c[p0 - N .. p0 + TILE), padded like the ones below
+    float2* pc = cs + ncp;
+    float2* sc = pc + ncp;
+    float* es = (float*)(sc + ncp);
+    float* pe = es + ncp;
+    float* se = pe + ncp;
     for (int i = threadIdx.x; i < nx; i += blockDim.x) xs[i] = ld_w(w, p0 - N - W1 + i, base, len);
     __syncthreads();
     for (int i = threadIdx.x; i < nc; i += blockDim.x) {
         const float2 a = xs[i + W1], b = xs[i];                 // x[m], x[m - N/2], m = p0 - N + i
-        cs[i] = make_float2(-__fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)), -__fmaf_rn(a.y, b.x, -__fmul_rn(a.x, b.y)));
-        es[i] = __fmul_rn(0.5f, __fmaf_rn(a.x, a.x, __fmul_rn(a.y, a.y)));
+        cs[PAD(i)] = make_float2(-__fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)), -__fmaf_rn(a.y, b.x, -__fmul_rn(a.x, b.y)));
+        es[PAD(i)] = __fmul_rn(0.5f, __fmaf_rn(a.x, a.x, __fmul_rn(a.y, a.y)));
     }
     __syncthreads();
-    // prefix (ascending) and suffix (descending) sums inside every aligned block: one thread per block
+    // prefix (ascending) and suffix (descending) sums inside every aligned block: one thread per (block, direction) chain
     const int nb1 = nc / W1, nb2 = nc / W2;
-    for (int b = threadIdx.x; b < nb1 + nb2; b += blockDim.x) {
-        if (b < nb1) {
-            const int o = b * W1;
-            float2 acc = cs[o];
-            pc[o] = acc;
-            for (int i = 1; i < W1; i++) { acc.x = __fadd_rn(acc.x, cs[o + i].x); acc.y = __fadd_rn(acc.y, cs[o + i].y); pc[o + i] = acc; }
-            acc = cs[o + W1 - 1];
-            sc[o + W1 - 1] = acc;
-            for (int i = W1 - 2; i >= 0; i--) { acc.x = __fadd_rn(acc.x, cs[o + i].x); acc.y = __fadd_rn(acc.y, cs[o + i].y); sc[o + i] = acc; }
+    for (int b = threadIdx.x; b < 2 * (nb1 + nb2); b += blockDim.x) {
+        const int dir = b & 1, bb = b >> 1;
+        if (bb < nb1) {
+            const int o = bb * W1;
+            if (!dir) {
+                float2 acc = cs[PAD(o)];
+                pc[PAD(o)] = acc;
+                for (int i = 1; i < W1; i++) { const float2 c = cs[PAD(o + i)]; acc.x = __fadd_rn(acc.x, c.x); acc.y = __fadd_rn(acc.y, c.y); pc[PAD(o + i)] = acc; }
+            } else {
+                float2 acc = cs[PAD(o + W1 - 1)];
+                sc[PAD(o + W1 - 1)] = acc;
+                for (int i = W1 - 2; i >= 0; i--) { const float2 c = cs[PAD(o + i)]; acc.x = __fadd_rn(acc.x, c.x); acc.y = __fadd_rn(acc.y, c.y); sc[PAD(o + i)] = acc; }
+            }
         } else {
-            const int o = (b - nb1) * W2;
-            float acc = es[o];
-            pe[o] = acc;
-            for (int i = 1; i < W2; i++) { acc = __fadd_rn(acc, es[o + i]); pe[o + i] = acc; }
-            acc = es[o + W2 - 1];
-            se[o + W2 - 1] = acc;
-            for (int i = W2 - 2; i >= 0; i--) { acc = __fadd_rn(acc, es[o + i]); se[o + i] = acc; }
+            const int o = (bb - nb1) * W2;
+            if (!dir) {
+                float acc = es[PAD(o)];
+                pe[PAD(o)] = acc;
+                for (int i = 1; i < W2; i++) { acc = __fadd_rn(acc, es[PAD(o + i)]); pe[PAD(o + i)] = acc; }
+            } else {
+                float acc = es[PAD(o + W2 - 1)];
+                se[PAD(o + W2 - 1)] = acc;
+                for (int i = W2 - 2; i >= 0; i--) { acc = __fadd_rn(acc, es[PAD(o + i)]); se[PAD(o + i)] = acc; }
+            }
         }
     }
     __syncthreads();
@@ -96,10 +106,10 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
     uint32_t* flags = p.flags + (size_t)s * p.flag_words;
     for (int j = threadIdx.x; j < TILE; j += blockDim.x) {
         const int i = N + j;
-        float2 P = pc[i];
-        if ((i + 1) % W1) { const float2 t = sc[i - W1 + 1]; P.x = __fadd_rn(P.x, t.x); P.y = __fadd_rn(P.y, t.y); }
-        float E = pe[i];
-        if ((i + 1) % W2) E = __fadd_rn(E, se[i - W2 + 1]);
+        float2 P = pc[PAD(i)];
+        if ((i + 1) % W1) { const float2 t = sc[PAD(i - W1 + 1)]; P.x = __fadd_rn(P.x, t.x); P.y = __fadd_rn(P.y, t.y); }
+        float E = pe[PAD(i)];
+        if ((i + 1) % W2) E = __fadd_rn(E, se[PAD(i - W2 + 1)]);
         const float m = __fdiv_rn(__fmaf_rn(P.x, P.x, __fmul_rn(P.y, P.y)), __fmul_rn(E, E));
         const long long n = p0 + j;
         const unsigned word = __ballot_sync(0xffffffffu, n < total && m >= p.threshold);
@@ -124,6 +134,63 @@ __device__ float2 sync_p_at(const float2* w, long long n, long long base, int le
     return make_float2(__fadd_rn(pre.x, suf.x), __fadd_rn(pre.y, suf.y));
 }
 
+// sync_p_at by a whole warp: the lanes fetch 32 terms at a time, the additions run in the same strict order (every lane does them
+// on shuffled terms, so the result is uniform) -- 32 loads in flight instead of one thread's dependent chain.
+__device__ float2 sync_p_at_warp(const float2* w, long long n, long long base, int len, int N, int lane)
+{
+    const int W1 = N / 2;
+    auto c_at = [&](long long m) {
+        const float2 a = ld_w(w, m, base, len), b = ld_w(w, m - W1, base, len);
+        return make_float2(-__fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)), -__fmaf_rn(a.y, b.x, -__fmul_rn(a.x, b.y)));
+    };
+    const long long b0 = n - (n % W1);
+    float2 pre = make_float2(0.f, 0.f);
+    bool first = true;
+    for (long long m0 = b0; m0 <= n; m0 += 32) {                 // ascending from the block's first element
+        const int cnt = (int)min(32ll, n - m0 + 1);
+        float2 c = make_float2(0.f, 0.f);
+        if (lane < cnt) c = c_at(m0 + lane);
+        for (int l = 0; l < cnt; l++) {
+            const float cx = __shfl_sync(0xffffffffu, c.x, l), cy = __shfl_sync(0xffffffffu, c.y, l);
+            if (first) { pre = make_float2(cx, cy); first = false; } else { pre.x = __fadd_rn(pre.x, cx); pre.y = __fadd_rn(pre.y, cy); }
+        }
+    }
+    if (n == b0 + W1 - 1) return pre;
+    float2 suf = make_float2(0.f, 0.f);
+    first = true;
+    for (long long m0 = b0 - 1; m0 >= n - W1 + 1; m0 -= 32) {    // descending from the previous block's last element
+        const int cnt = (int)min(32ll, m0 - (n - W1 + 1) + 1);
+        float2 c = make_float2(0.f, 0.f);
+        if (lane < cnt) c = c_at(m0 - lane);
+        for (int l = 0; l < cnt; l++) {
+            const float cx = __shfl_sync(0xffffffffu, c.x, l), cy = __shfl_sync(0xffffffffu, c.y, l);
+            if (first) { suf = make_float2(cx, cy); first = false; } else { suf.x = __fadd_rn(suf.x, cx); suf.y = __fadd_rn(suf.y, cy); }
+        }
+    }
+    return make_float2(__fadd_rn(pre.x, suf.x), __fadd_rn(pre.y, suf.y));
+}
+
+// first flagged position in [i, end), else end: the lanes look at 32 flag words (1024 positions) per round
+__device__ long long sync_next_flag(const uint32_t* flags, long long flo, long long i, long long end, int lane)
+{
+    if (i >= end) return end;
+    const long long w0 = (i - flo) >> 5, we = (end - 1 - flo) >> 5;
+    const int sh = (int)((i - flo) & 31);
+    for (long long wb = w0; wb <= we; wb += 32) {
+        const long long wj = wb + lane;
+        uint32_t word = wj <= we ? flags[wj] : 0u;
+        if (wj == w0) word &= 0xffffffffu << sh;                // positions below i
+        const unsigned m = __ballot_sync(0xffffffffu, word != 0u);
+        if (m) {
+            const int l = __ffs(m) - 1;
+            const uint32_t wv = __shfl_sync(0xffffffffu, word, l);
+            const long long n = flo + ((wb + l) << 5) + (__ffs(wv) - 1);
+            return n < end ? n : end;
+        }
+    }
+    return end;
+}
+
 __device__ __forceinline__ double sync_phase(const SyncSeg* segs, int nseg, long long n, int N)
 {
     int k = -1;
@@ -132,10 +199,12 @@ __device__ __forceinline__ double sync_phase(const SyncSeg* segs, int nseg, long
     return segs[k].ph + (double)(n - segs[k].t) * (-2.0 / N) * (double)segs[k].f;
 }
 
-// One thread per stream: everything that is sequential in the stream, on the sparse events only.
-__global__ void __launch_bounds__(64) sync_scan_kernel(SyncParams p)
+// One WARP per stream: everything that is sequential in the stream, on the sparse events only.  The state machines run
+// replicated in every lane (uniform control flow; identical values written to the per-stream lists by every lane); the lanes
+// share the two things that touch memory in bulk: the search for the next flagged position and the window sum at a trigger.
+__global__ void __launch_bounds__(128) sync_scan_kernel(SyncParams p)
 {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (s >= p.n_streams) return;
     SyncState st = p.st[s];
     const int N = p.N, cp = p.cp, FS = p.FS, D = N + cp;
@@ -155,17 +224,14 @@ __global__ void __launch_bounds__(64) sync_scan_kernel(SyncParams p)
     // ---- plateau_detector_fb(max_len = cp, threshold): skip the zero words, then walk the run
     long long i = st.scan_pos > c0 ? st.scan_pos : c0;
     while (i < scan_end) {
-        const long long wi = (i - flo) >> 5;
-        const uint32_t word = flags[wi] >> ((i - flo) & 31);
-        if (!word) { i = flo + ((wi + 1) << 5); if (i > scan_end) i = scan_end; continue; }   // never past what the reference's i++ reaches
-        i += __ffs(word) - 1;
+        i = sync_next_flag(flags, flo, i, scan_end, lane);       // never past scan_end: what the reference's i++ reaches
         if (i >= scan_end) break;
         int k = 1;
         for (; k < cp; k++) if (!flag(i + k)) break;
         if (k > 1) {
             const long long t = i + k / 2;
             if (nraw < p.trig_cap) raw[nraw++] = t; else err = 1;
-            const float2 P = sync_p_at(w, t, base, len, N);
+            const float2 P = sync_p_at_warp(w, t, base, len, N, lane);
             const float f = (float)atan2((double)P.y, (double)P.x);
             double ph = sync_phase(segs, nseg, t - 1, N) + (-2.0 / N) * (double)f;
             ph = fmod(ph + 3.14159265358979323846, 6.28318530717958647692);
@@ -244,7 +310,11 @@ __global__ void __launch_bounds__(64) sync_scan_kernel(SyncParams p)
     }
     st.chunk_pos = c1;
     // `fixed` is in visiting order; triggers moved backwards can break the ascending order: sort (insertion, a handful of entries)
-    for (int a = 1; a < nfixed; a++) { const long long v = fixed[a]; int b = a - 1; while (b >= 0 && fixed[b] > v) { fixed[b + 1] = fixed[b]; b--; } fixed[b + 1] = v; }
+    // (one lane: the only place where the list is MOVED in memory; everywhere else the lanes write identical values)
+    __syncwarp();
+    if (lane == 0)
+        for (int a = 1; a < nfixed; a++) { const long long v = fixed[a]; int b = a - 1; while (b >= 0 && fixed[b] > v) { fixed[b + 1] = fixed[b]; b--; } fixed[b + 1] = v; }
+    __syncwarp();
     // ---- header_payload_demux: a trigger starts a frame unless one is being copied; frames complete when their last sample is in
     long long* starts = p.starts + (size_t)s * p.frames_cap;
     int nfr = 0, npend = 0;
@@ -281,8 +351,10 @@ __global__ void __launch_bounds__(64) sync_scan_kernel(SyncParams p)
     st.nsegc = 0;
     for (int a = ks; a < nseg; a++) { if (st.nsegc < DTL_SYNC_SEGC) st.segc[st.nsegc++] = segs[a]; else err = 1; }
     st.base_cur = base; st.len_cur = len;
-    p.st[s] = st;
-    if (err) atomicOr(p.err, err == 2 ? 64 : 1024);
+    if (lane == 0) {
+        p.st[s] = st;
+        if (err) atomicOr(p.err, err == 2 ? 64 : 1024);
+    }
 }
 
 // Frame j of stream s: out[q] = x[t + q - D] * exp(j phase[t + q]).  Unused frame slots are zero-filled and flagged invalid.
@@ -305,13 +377,37 @@ __global__ void __launch_bounds__(256) sync_cut_kernel(SyncParams p)
     const long long base = st.base_cur, t = p.starts[(size_t)s * p.frames_cap + j];
     const int len = st.len_cur, nseg = p.n_seg[s];
     const float2* w = p.w_new + (size_t)s * p.w_cap;
-    const SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;
+    // the oscillator's segments that can matter for this CTA's samples, in shared memory (a handful per call)
+    __shared__ SyncSeg sseg[16];
+    __shared__ int s_n;
+    if (threadIdx.x == 0) {
+        const SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;
+        const long long lo = t + q0, hi = t + min(q0 + 1024, FS) - 1;
+        int first = -1, n = 0;
+        for (int i = 0; i < nseg; i++) if (segs[i].t <= lo) first = i;        // the segment in force at the first sample
+        bool over = false;
+        for (int i = first < 0 ? 0 : first; i < nseg && segs[i].t <= hi; i++) { if (n < 16) sseg[n++] = segs[i]; else over = true; }
+        s_n = over ? -1 : n;                                    // more than 16 segments inside 1024 samples (a burst of false triggers): search the global list
+    }
+    __syncthreads();
+    const int ns = s_n;
+    const double w0 = -2.0 / N, inv2pi = 0.15915494309189533577, twopi = 6.28318530717958647692;
     for (int q = q0 + threadIdx.x; q < min(q0 + 1024, FS); q += blockDim.x) {
         const float2 y = ld_w(w, t + q - D, base, len);
-        const double ph = sync_phase(segs, nseg, t + q, N);
-        double sn, cs;
-        sincos(ph, &sn, &cs);
-        const float c = (float)cs, sf = (float)sn;
+        const long long n = t + q;
+        int k = -1;
+        const SyncSeg* sl = sseg;
+        int nsl = ns;
+        if (ns < 0) { sl = p.segs + (size_t)s * p.seg_cap; nsl = nseg; }
+        for (int i = 0; i < nsl; i++) { if (sl[i].t <= n) k = i; else break; }
+        // phase in double as the oscillator accumulates it, reduced to [-pi, pi] in double; sine / cosine in fp32 (the samples are
+        // fp32: 1e-6 absolute, the tolerance on the mixed samples is 1e-4)
+        float c = 1.f, sf = 0.f;
+        if (k >= 0) {
+            const double ph = sl[k].ph + (double)(n - sl[k].t) * w0 * (double)sl[k].f;
+            const float r = (float)(ph - twopi * rint(ph * inv2pi));
+            __sincosf(r, &sf, &c);
+        }
         out[q] = make_float2(__fmaf_rn(y.x, c, -__fmul_rn(y.y, sf)), __fmaf_rn(y.x, sf, __fmul_rn(y.y, c)));
     }
 }
@@ -332,7 +428,11 @@ cudaError_t launch_sync_reset(cudaStream_t st, SyncState* state, int n)
     return cudaGetLastError();
 }
 
-size_t sync_metric_smem(int N) { const int T = N > 1024 ? N : 1024; return (size_t)(T + N + N / 2) * 8 + 3 * (size_t)(T + N) * 8 + 3 * (size_t)(T + N) * 4; }
+size_t sync_metric_smem(int N)
+{
+    const int T = N > 1024 ? N : 1024, nc = T + N, ncp = nc + (nc >> 5) + 1;      // PAD of sync_metric_kernel
+    return (size_t)(T + N + N / 2) * 8 + 3 * (size_t)ncp * 8 + 3 * (size_t)ncp * 4 + 16;
+}
 
 cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches)
 {
@@ -341,7 +441,7 @@ cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches)
     sync_append_kernel<<<dim3((unsigned)((max_len + 2047) / 2048 < 64 ? (max_len + 2047) / 2048 : 64), p.n_streams), 256, 0, st>>>(p);
     const int tiles = (int)((p.T + p.keep_cap + 1023) / 1024 + 1);
     sync_metric_kernel<1024><<<dim3(tiles, p.n_streams), 256, sync_metric_smem(p.N), st>>>(p);
-    sync_scan_kernel<<<(p.n_streams + 63) / 64, 64, 0, st>>>(p);
+    sync_scan_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
     sync_cut_kernel<<<dim3((p.FS + 1023) / 1024, p.frames_cap, p.n_streams), 256, 0, st>>>(p);
     if (launches) *launches += 4;
     return cudaGetLastError();
