@@ -41,11 +41,12 @@ __global__ void __launch_bounds__(256) sync_append_kernel(SyncParams p)
 // ---- Schmidl & Cox metric, one bit per position ------------------------------------------------------------------------
 // Tile of TILE positions starting at a multiple of TILE (global index).  Shared memory: x[TILE + N + N/2], c / prefix / suffix
 // of c [TILE + N] (float2), e / prefix / suffix of e [TILE + N] (float).
-template <int TILE>
+// NFIX: fft_len known at compile time (64: the reference's PHY) so that the chains below unroll; 0 = any fft_len
+template <int TILE, int NFIX>
 __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
 {
     extern __shared__ __align__(16) unsigned char sm[];
-    const int N = p.N, W1 = N / 2, W2 = N, s = blockIdx.y;
+    const int N = NFIX ? NFIX : p.N, W1 = N / 2, W2 = N, s = blockIdx.y;
     const SyncState st = p.st[s];
     const int len = st.keep_len + p.T;
     const long long base = st.base_next;                        // global index of W[0] for this call
@@ -82,10 +83,12 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
             if (!dir) {
                 float2 acc = cs[PAD(o)];
                 pc[PAD(o)] = acc;
+#pragma unroll 16
                 for (int i = 1; i < W1; i++) { const float2 c = cs[PAD(o + i)]; acc.x = __fadd_rn(acc.x, c.x); acc.y = __fadd_rn(acc.y, c.y); pc[PAD(o + i)] = acc; }
             } else {
                 float2 acc = cs[PAD(o + W1 - 1)];
                 sc[PAD(o + W1 - 1)] = acc;
+#pragma unroll 16
                 for (int i = W1 - 2; i >= 0; i--) { const float2 c = cs[PAD(o + i)]; acc.x = __fadd_rn(acc.x, c.x); acc.y = __fadd_rn(acc.y, c.y); sc[PAD(o + i)] = acc; }
             }
         } else {
@@ -93,10 +96,12 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
             if (!dir) {
                 float acc = es[PAD(o)];
                 pe[PAD(o)] = acc;
+#pragma unroll 16
                 for (int i = 1; i < W2; i++) { acc = __fadd_rn(acc, es[PAD(o + i)]); pe[PAD(o + i)] = acc; }
             } else {
                 float acc = es[PAD(o + W2 - 1)];
                 se[PAD(o + W2 - 1)] = acc;
+#pragma unroll 16
                 for (int i = W2 - 2; i >= 0; i--) { acc = __fadd_rn(acc, es[PAD(o + i)]); se[PAD(o + i)] = acc; }
             }
         }
@@ -440,13 +445,19 @@ cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches)
     const int max_len = p.w_cap;
     sync_append_kernel<<<dim3((unsigned)((max_len + 2047) / 2048 < 64 ? (max_len + 2047) / 2048 : 64), p.n_streams), 256, 0, st>>>(p);
     const int tiles = (int)((p.T + p.keep_cap + 1023) / 1024 + 1);
-    sync_metric_kernel<1024><<<dim3(tiles, p.n_streams), 256, sync_metric_smem(p.N), st>>>(p);
+    if (p.N == 64) sync_metric_kernel<1024, 64><<<dim3(tiles, p.n_streams), 256, sync_metric_smem(p.N), st>>>(p);
+    else sync_metric_kernel<1024, 0><<<dim3(tiles, p.n_streams), 256, sync_metric_smem(p.N), st>>>(p);
     sync_scan_kernel<<<(p.n_streams + 3) / 4, 128, 0, st>>>(p);
     sync_cut_kernel<<<dim3((p.FS + 1023) / 1024, p.frames_cap, p.n_streams), 256, 0, st>>>(p);
     if (launches) *launches += 4;
     return cudaGetLastError();
 }
 
-cudaError_t init_kernels_sync() { return set_max_dyn_smem(sync_metric_kernel<1024>); }
+cudaError_t init_kernels_sync()
+{
+    cudaError_t e = set_max_dyn_smem(sync_metric_kernel<1024, 0>);
+    if (e == cudaSuccess) e = set_max_dyn_smem(sync_metric_kernel<1024, 64>);
+    return e;
+}
 
 } // namespace dtl
