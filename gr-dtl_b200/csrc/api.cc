@@ -1488,10 +1488,18 @@ dtl_status rx_device(dtl_b200* h, Stage& sg, int in_kind, const float2* d_in, co
 // DTL_MEM_HOST with many streams: the batch is cut into chunks of whole streams (streams are independent; the
 // per-stream state is indexed by stream).  Chunk c+1's host->device copies run on the copy stream under chunk c's
 // kernels, the small device->host result copies of chunk c on a third stream; two input staging buffers alternate.
+dtl_status rx_iq_device(dtl_b200* h, Stage& sg, const float2* d_iq, int S, int F, dtl_frame_meta* d_meta, float2* d_taps,
+                        dtl_header_result* d_hres, dtl_frame_result* d_res, uint8_t* d_bytes, int bytes_cap, int* d_nb,
+                        dtl_tb_result* d_tbs, int tb_cap, int* d_nt, int* d_fcrc, const int* valid);
+
+// in_kind 0 / 1: IQ / frequency-domain symbols with the caller's taps and tags; in_kind 2: IQ ALONE (dtl_b200_rx_iq): nothing
+// but the samples is uploaded, the header branch of every chunk produces its taps and tags on the device (meta_out / hres come back).
 dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
                              int S, int F, int Sc, dtl_frame_result* res, uint8_t* bytes, int bytes_cap, int* nbytes,
-                             dtl_tb_result* tbs, int tb_cap, int* ntbs, int* frame_crc)
+                             dtl_tb_result* tbs, int tb_cap, int* ntbs, int* frame_crc,
+                             dtl_frame_meta* meta_out = nullptr, dtl_header_result* hres = nullptr)
 {
+    const bool iq_only = in_kind == 2;
     if (!h->copy_stream) {
         CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&h->out_stream, cudaStreamNonBlocking));
@@ -1500,7 +1508,7 @@ dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const fl
             CK(cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming));
         }
     }
-    const size_t in_per_frame = in_kind == 0 ? (size_t)h->frame_samples : (size_t)h->L * h->N;
+    const size_t in_per_frame = in_kind != 1 ? (size_t)h->frame_samples : (size_t)h->L * h->N;
     const size_t nmax = (size_t)Sc * F;
     Stage sg(h, DTL_MEM_DEVICE);
     // full-batch device outputs (small), per-chunk inputs (double-buffered)
@@ -1510,6 +1518,8 @@ dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const fl
     dtl_tb_result* d_tbs = tbs ? sg.scratch<dtl_tb_result>(SL_TBS_OUT, (size_t)S * tb_cap) : nullptr;
     int* d_nt = ntbs ? sg.scratch<int>(SL_NTBS, (size_t)S) : nullptr;
     int* d_fcrc = frame_crc ? sg.scratch<int>(SL_FCRC, (size_t)S * F) : nullptr;
+    dtl_frame_meta* d_meta_all = iq_only ? sg.scratch<dtl_frame_meta>(SL_HMETA, (size_t)S * F) : nullptr;
+    dtl_header_result* d_hres_all = iq_only && hres ? sg.scratch<dtl_header_result>(SL_HRES, (size_t)S * F) : nullptr;
     if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "staging");
     for (int i = 0; i < 2; i++) {
         CK(h->pipe_in[i][0].ensure(nmax * in_per_frame * sizeof(float2) + 16));
@@ -1527,15 +1537,23 @@ dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const fl
         const size_t f0 = (size_t)s0 * F, n = (size_t)Sn * F;
         if (c >= 2) CK(cudaStreamWaitEvent(h->copy_stream, h->ev_done[b], 0));     // staging buffer b is free again
         CK(cudaMemcpyAsync(h->pipe_in[b][0].p, (const float2*)in + f0 * in_per_frame, n * in_per_frame * sizeof(float2), cudaMemcpyHostToDevice, h->copy_stream));
-        CK(cudaMemcpyAsync(h->pipe_in[b][1].p, (const float2*)taps + f0 * h->N, n * h->N * sizeof(float2), cudaMemcpyHostToDevice, h->copy_stream));
-        CK(cudaMemcpyAsync(h->pipe_in[b][2].p, meta + f0, n * sizeof(dtl_frame_meta), cudaMemcpyHostToDevice, h->copy_stream));
+        if (!iq_only) {
+            CK(cudaMemcpyAsync(h->pipe_in[b][1].p, (const float2*)taps + f0 * h->N, n * h->N * sizeof(float2), cudaMemcpyHostToDevice, h->copy_stream));
+            CK(cudaMemcpyAsync(h->pipe_in[b][2].p, meta + f0, n * sizeof(dtl_frame_meta), cudaMemcpyHostToDevice, h->copy_stream));
+        }
         CK(cudaEventRecord(h->ev_h2d[b], h->copy_stream));
         CK(cudaStreamWaitEvent(h->stream, h->ev_h2d[b], 0));
         h->s_off = s0;
-        s = rx_device(h, sg, in_kind, (const float2*)h->pipe_in[b][0].p, (const float2*)h->pipe_in[b][1].p,
-                      (const dtl_frame_meta*)h->pipe_in[b][2].p, Sn, F, d_res ? d_res + f0 : nullptr,
-                      d_bytes ? d_bytes + (size_t)s0 * bytes_cap : nullptr, bytes_cap, d_nb ? d_nb + s0 : nullptr,
-                      d_tbs ? d_tbs + (size_t)s0 * tb_cap : nullptr, tb_cap, d_nt ? d_nt + s0 : nullptr, d_fcrc ? d_fcrc + f0 : nullptr);
+        if (iq_only)
+            s = rx_iq_device(h, sg, (const float2*)h->pipe_in[b][0].p, Sn, F, d_meta_all + f0, (float2*)h->pipe_in[b][1].p,
+                             d_hres_all ? d_hres_all + f0 : nullptr, d_res ? d_res + f0 : nullptr,
+                             d_bytes ? d_bytes + (size_t)s0 * bytes_cap : nullptr, bytes_cap, d_nb ? d_nb + s0 : nullptr,
+                             d_tbs ? d_tbs + (size_t)s0 * tb_cap : nullptr, tb_cap, d_nt ? d_nt + s0 : nullptr, d_fcrc ? d_fcrc + f0 : nullptr, nullptr);
+        else
+            s = rx_device(h, sg, in_kind, (const float2*)h->pipe_in[b][0].p, (const float2*)h->pipe_in[b][1].p,
+                          (const dtl_frame_meta*)h->pipe_in[b][2].p, Sn, F, d_res ? d_res + f0 : nullptr,
+                          d_bytes ? d_bytes + (size_t)s0 * bytes_cap : nullptr, bytes_cap, d_nb ? d_nb + s0 : nullptr,
+                          d_tbs ? d_tbs + (size_t)s0 * tb_cap : nullptr, tb_cap, d_nt ? d_nt + s0 : nullptr, d_fcrc ? d_fcrc + f0 : nullptr);
         h->s_off = 0;
         if (s != DTL_OK) break;
         CK(cudaEventRecord(h->ev_done[b], h->stream));
@@ -1546,6 +1564,8 @@ dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const fl
         if (tbs) CK(cudaMemcpyAsync(tbs + (size_t)s0 * tb_cap, d_tbs + (size_t)s0 * tb_cap, (size_t)Sn * tb_cap * sizeof(dtl_tb_result), cudaMemcpyDeviceToHost, h->out_stream));
         if (ntbs) CK(cudaMemcpyAsync(ntbs + s0, d_nt + s0, (size_t)Sn * sizeof(int), cudaMemcpyDeviceToHost, h->out_stream));
         if (frame_crc) CK(cudaMemcpyAsync(frame_crc + f0, d_fcrc + f0, n * sizeof(int), cudaMemcpyDeviceToHost, h->out_stream));
+        if (iq_only && meta_out) CK(cudaMemcpyAsync(meta_out + f0, d_meta_all + f0, n * sizeof(dtl_frame_meta), cudaMemcpyDeviceToHost, h->out_stream));
+        if (iq_only && hres) CK(cudaMemcpyAsync(hres + f0, d_hres_all + f0, n * sizeof(dtl_header_result), cudaMemcpyDeviceToHost, h->out_stream));
     }
     cudaError_t e1 = cudaStreamSynchronize(h->copy_stream), e2 = cudaStreamSynchronize(h->out_stream);
     dtl_status s2 = dtl_b200_sync(h);
@@ -1678,6 +1698,16 @@ extern "C" dtl_status dtl_b200_rx_iq(dtl_b200* h, const float* iq, int32_t n_str
     const size_t n = (size_t)S * F;
     dtl_status s = ensure_streams(h, S);
     if (s != DTL_OK) return s;
+    if (mem == DTL_MEM_HOST && F > 0) {              // many streams from host memory: chunks of whole streams, copies under compute
+        const size_t per_stream = (size_t)F * (size_t)h->frame_samples * sizeof(float2);
+        static size_t chunk_mb = 0;
+        if (!chunk_mb) { const char* e = getenv("DTL_HOST_CHUNK_MB"); chunk_mb = e && atoi(e) > 0 ? (size_t)atoi(e) : 48; }
+        int Sc = (int)std::max<size_t>(1, (chunk_mb << 20) / std::max<size_t>(per_stream, 1));
+        if (S >= 4 * Sc || (S >= 8 && per_stream * S >= ((size_t)16 << 20))) {
+            Sc = std::min(Sc, (S + 3) / 4);
+            return rx_host_pipelined(h, 2, iq, nullptr, nullptr, S, F, Sc, res, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, frame_crc, meta_out, hres);
+        }
+    }
     Stage sg(h, mem);
     const float2* d_iq = sg.in(SL_IQ, (const float2*)iq, n * h->frame_samples);
     dtl_frame_meta* d_meta = meta_out ? sg.out(SL_HMETA, meta_out, n) : sg.scratch<dtl_frame_meta>(SL_HMETA, n);
