@@ -608,11 +608,13 @@ def run_b200(a):
         for _ in range(3):
             step_stream()
         rx.sync()
-        sync_ms = rx.stage_times(reset=True)["sync"][0] / 3
+        st3 = rx.stage_times(reset=True)
+        sync_ms = st3["sync"][0] / 3
         rx.profile(False)
         from_stream = {"value": samples_all / (ms_st * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_st,
                        "sync_front_end_ms_per_step": sync_ms, "frames_found_per_call": int(nfr.sum()), "frames_sent_per_call": S * F,
                        "headers_parsed_per_call": int(hdr3.sum()),
+                       "stage_ms_per_step": {k: v[0] / 3 for k, v in st3.items() if v[0] > 0},
                        "api": "dtl_b200_rx_stream(mem=DTL_MEM_DEVICE): continuous IQ; Schmidl & Cox timing + fine CFO, trigger "
                               "regulariser, frame cut, then the path from IQ alone"}
         del out3
