@@ -5,6 +5,8 @@
 //   ofdm_adaptive_frame_equalizer_vcvc::make    include/gnuradio/dtl/ofdm_adaptive_frame_equalizer_vcvc.h:30-36
 //   ofdm_adaptive_constellation_soft_cf::make   include/gnuradio/dtl/ofdm_adaptive_constellation_soft_cf.h:28
 //   ofdm_adaptive_fec_decoder::make             include/gnuradio/dtl/ofdm_adaptive_fec_decoder.h:27
+//   ofdm_adaptive_constellation_decoder_cb::make include/gnuradio/dtl/ofdm_adaptive_constellation_decoder_cb.h:34-35
+//   ofdm_adaptive_chunks_to_symbols_bc::make     include/gnuradio/dtl/ofdm_adaptive_chunks_to_symbols_bc.h:32-35
 //   fec_enc / fec_dec / make_ldpc_{en,de}coders include/gnuradio/dtl/fec.h:17-35
 // In a gr-dtl tree these declarations ARE the reference's public headers (unchanged); only lib/dtl/*_impl.cc change.  Here the
 // configuration objects (equaliser, feedback decision, SNR estimator) carry parameters only: their arithmetic runs on the GPU.
@@ -123,6 +125,20 @@ class ofdm_adaptive_constellation_soft_cf : virtual public gr::block
 public:
     typedef std::shared_ptr<ofdm_adaptive_constellation_soft_cf> sptr;
     static sptr make(const std::vector<constellation_type_t>& constellations, const std::string& len_key);
+};
+
+// lib/dtl side: include/gnuradio/dtl/ofdm_adaptive_constellation_decoder_cb.h:23-37, ofdm_adaptive_chunks_to_symbols_bc.h:23-38
+class ofdm_adaptive_constellation_decoder_cb : virtual public gr::tagged_stream_block
+{
+public:
+    typedef std::shared_ptr<ofdm_adaptive_constellation_decoder_cb> sptr;
+    static sptr make(const std::vector<constellation_type_t>& constellations, const std::string& tsb_tag_key);
+};
+class ofdm_adaptive_chunks_to_symbols_bc : virtual public gr::tagged_stream_block
+{
+public:
+    typedef std::shared_ptr<ofdm_adaptive_chunks_to_symbols_bc> sptr;
+    static sptr make(const std::vector<constellation_type_t>& constellations, const std::string& tsb_tag_key);
 };
 
 class fec_enc

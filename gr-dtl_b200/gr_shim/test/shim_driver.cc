@@ -198,6 +198,43 @@ int main(int argc, char** argv)
             }
         }
 
+        // ---- python/dtl/qa_ofdm_adaptive_chunks_to_symbols_bc.py:39-63: vector_source_b -> chunks_to_symbols_bc -> decoder_cb, one
+        // tagged stream per constellation ("md_chunks" u8 [n_md][md_len], "md_cnst" i32 [n_md])
+        std::vector<gr_complex> md_syms;
+        std::vector<unsigned char> md_out;
+        std::string md_error;
+        {
+            const auto mc = vec<unsigned char>(sc, "md_chunks");
+            const auto mk = vec<int32_t>(sc, "md_cnst");
+            if (!mk.empty()) {
+                const int len = (int)(mc.size() / mk.size());
+                std::vector<constellation_type_t> all;
+                for (int32_t c : vec<int32_t>(sc, "cnsts")) all.push_back((constellation_type_t)c);
+                auto mod = ofdm_adaptive_chunks_to_symbols_bc::make(all, "len_tag");
+                auto demod = ofdm_adaptive_constellation_decoder_cb::make(all, "len_tag");
+                for (size_t k = 0; k < mk.size() && md_error.empty(); k++) {
+                    auto tagit = [&](gr::block& b, bool with_cnst) {
+                        gr::tag_t t; t.offset = b.nitems_read(0);
+                        if (with_cnst) { t.key = pmt::mp("constellation_tag_key"); t.value = pmt::from_long(mk[k]); b.in_tags[0].push_back(t); }
+                        t.key = pmt::mp("len_tag"); t.value = pmt::from_long(len); b.in_tags[0].push_back(t);
+                    };
+                    std::vector<gr_complex> syms(len);
+                    std::vector<unsigned char> back(len);
+                    gr_vector_int nin{ len };
+                    try {
+                        tagit(*mod, mk[k] != 0);
+                        gr_vector_const_void_star i1{ &mc[k * len] }; gr_vector_void_star o1{ syms.data() };
+                        if (mod->run(len, nin, i1, o1) != len) throw std::runtime_error("chunks_to_symbols: short output");
+                        tagit(*demod, true);
+                        gr_vector_const_void_star i2{ syms.data() }; gr_vector_void_star o2{ back.data() };
+                        if (demod->run(len, nin, i2, o2) != len) throw std::runtime_error("decoder_cb: short output");
+                    } catch (const std::exception& e) { md_error = e.what(); break; }
+                    md_syms.insert(md_syms.end(), syms.begin(), syms.end());
+                    md_out.insert(md_out.end(), back.begin(), back.end());
+                }
+            }
+        }
+
         FILE* fo = fopen(argv[2], "wb");
         if (!fo) throw std::runtime_error("cannot open result file");
         write_rec(fo, "error", error.data(), error.size());
@@ -217,6 +254,9 @@ int main(int argc, char** argv)
         write_rec(fo, "cw_nit", cw_nit.data(), cw_nit.size() * 4);
         write_rec(fo, "cw_wire", cw_wire.data(), cw_wire.size());
         write_rec(fo, "code_nk", code_nk.data(), code_nk.size() * 4);
+        write_rec(fo, "md_syms", md_syms.data(), md_syms.size() * sizeof(gr_complex));
+        write_rec(fo, "md_out", md_out.data(), md_out.size());
+        write_rec(fo, "md_error", md_error.data(), md_error.size());
         fclose(fo);
         return 0;
     } catch (const std::exception& e) {

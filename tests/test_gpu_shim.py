@@ -120,3 +120,29 @@ def test_missing_constellation_tag_throws_what_the_reference_throws(tmp_path):
     got = run_driver(tmp_path, scenario(ocfg, 2, ocfg.rx_demod(t["iq"]), t["taps"], meta, False))
     assert got["error"] == b"Missing constellation tag."          # frame_equalizer_vcvc_impl.cc:150-152
     assert np.frombuffer(got["emitted"], dtype=np.int32).size == 1
+
+
+def test_chunks_to_symbols_and_decoder_cb_blocks(tmp_path):
+    """python/dtl/qa_ofdm_adaptive_chunks_to_symbols_bc.py:39-63 through the shims: [0,1,2,3,3,2,1,0] in QPSK comes back, the
+    symbols in between are the constellation's points; the same for every constellation; a stream without the constellation
+    tag throws "Constellation not found" (chunks_to_symbols_bc_impl.cc:69-71)."""
+    ocfg = make_oracle_cfg(cnsts=(1, 2, 3, 4, 5, 6))
+    t = ocfg.tx_batch(1, 1, seed=1, cnst=2, snr_db=30.0)
+    rng = np.random.default_rng(12)
+    bps = {1: 1, 2: 2, 3: 3, 4: 4, 5: 6, 6: 8}
+    cn = [2, 1, 3, 4, 5, 6]
+    chunks = np.stack([np.array([0, 1, 2, 3, 3, 2, 1, 0], dtype=np.uint8)] +
+                      [rng.integers(0, 1 << bps[c], 8, dtype=np.uint8) for c in cn[1:]])
+    recs = scenario(ocfg, 0, np.zeros((0, 20, 64), np.complex64), np.zeros((0, 64), np.complex64), t["meta"][:0], False)
+    recs["md_chunks"] = chunks
+    recs["md_cnst"] = np.asarray(cn, dtype=np.int32)
+    got = run_driver(tmp_path, recs)
+    assert got["md_error"] == b""
+    back = np.frombuffer(got["md_out"], dtype=np.uint8).reshape(len(cn), 8)
+    assert np.array_equal(back, chunks) and list(back[0]) == [0, 1, 2, 3, 3, 2, 1, 0]
+    syms = np.frombuffer(got["md_syms"], dtype=np.complex64).reshape(len(cn), 8)
+    for k, c in enumerate(cn):
+        assert np.array_equal(syms[k].view(np.uint32), orc.map_chunks(c, chunks[k]).astype(np.complex64).view(np.uint32)), c
+    recs["md_cnst"] = np.asarray([0], dtype=np.int32)
+    recs["md_chunks"] = chunks[:1]
+    assert run_driver(tmp_path, recs)["md_error"] == b"Constellation not found"

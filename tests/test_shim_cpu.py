@@ -23,6 +23,8 @@ def test_shim_exports_the_reference_factories():
                 "gr::dtl::ofdm_adaptive_feedback_decision::make(",              # ofdm_adaptive_feedback_decision.h:49-52
                 "gr::dtl::ofdm_adaptive_constellation_soft_cf::make(",          # ofdm_adaptive_constellation_soft_cf.h:28
                 "gr::dtl::ofdm_adaptive_fec_decoder::make(",                    # ofdm_adaptive_fec_decoder.h:27
+                "gr::dtl::ofdm_adaptive_constellation_decoder_cb::make(",       # ofdm_adaptive_constellation_decoder_cb.h:34-35
+                "gr::dtl::ofdm_adaptive_chunks_to_symbols_bc::make(",           # ofdm_adaptive_chunks_to_symbols_bc.h:32-35
                 "gr::dtl::make_ldpc_decoders(", "gr::dtl::make_ldpc_encoders("):    # fec.h:33-35
         assert sym in out, sym
     # the only undefined dtl_b200_* symbols are C ABI entry points declared in include/dtl_b200.h
@@ -31,7 +33,8 @@ def test_shim_exports_the_reference_factories():
     used = sorted({l.split()[-1] for l in und.splitlines() if "dtl_b200_" in l})
     header = open(os.path.join(ROOT, "include", "dtl_b200.h")).read()
     assert used and all(u + "(" in header for u in used), used
-    assert {"dtl_b200_equalize", "dtl_b200_soft_demap", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode", "dtl_b200_ldpc_encode"} <= set(used)
+    assert {"dtl_b200_equalize", "dtl_b200_soft_demap", "dtl_b200_hard_demap", "dtl_b200_map", "dtl_b200_fec_decode", "dtl_b200_ldpc_decode",
+            "dtl_b200_ldpc_encode"} <= set(used)
 
 
 def test_shim_sources_do_not_touch_the_oracle_or_the_reference():
