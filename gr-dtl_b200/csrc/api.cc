@@ -20,11 +20,14 @@ namespace {
 std::mutex g_err_mu;
 std::string g_create_err;
 
+unsigned long long g_alloc_gen = 0;      // bumped whenever a device buffer moves: captured graphs hold raw pointers (RxGraph)
+
 struct DevBuf {
     void* p = nullptr; size_t cap = 0;
     cudaError_t ensure(size_t n)
     {
         if (n <= cap) return cudaSuccess;
+        g_alloc_gen++;
         if (p) { cudaError_t e = cudaFree(p); p = nullptr; cap = 0; if (e != cudaSuccess) return e; }
         size_t want = n + n / 8 + 256;
         cudaError_t e = cudaMalloc(&p, want);
@@ -46,11 +49,26 @@ enum Slot {
 
 } // namespace
 
+// The one-frame call (S = 1, F = 1, DTL_MEM_HOST: what a block shim does per work()) as a CUDA graph: ~15 dependent launches
+// and the stream forks / joins around them become one cudaGraphLaunch.  Captured from the ordinary code path after two warm-up
+// calls (every scratch buffer has its size by then); replays stage through page-locked buffers of the handle.
+struct RxGraph {
+    cudaGraphExec_t exec = nullptr;
+    int in_kind = -1, bytes_cap = 0, tb_cap = 0, mask = 0, warm = 0;
+    unsigned long long gen = 0;
+    bool failed = false;
+    uint64_t launches = 0;
+    unsigned char* pin = nullptr; size_t pin_bytes = 0;
+    size_t o_in = 0, o_taps = 0, o_meta = 0, o_res = 0, o_bytes = 0, o_nb = 0, o_tbs = 0, o_nt = 0, o_fcrc = 0;
+    void drop() { if (exec) cudaGraphExecDestroy(exec); exec = nullptr; warm = 0; }
+};
+
 struct dtl_b200 {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
     std::string err;
     uint64_t launches = 0;
+    RxGraph rxg;
     Prof prof;
     // configuration (deep copies)
     int N = 0, cp = 0, L = 0, H = 1, cap = 0, max_bps = 0, fec_enabled = 0;
@@ -390,6 +408,8 @@ extern "C" void dtl_b200_destroy(dtl_b200* h)
     if (!h) return;
     if (cudaSetDevice(h->device) != cudaSuccess) { cudaGetLastError(); delete h; return; }   // runtime unloading: nothing to free
     if (h->stream) cudaStreamSynchronize(h->stream);
+    h->rxg.drop();
+    if (h->rxg.pin) cudaFreeHost(h->rxg.pin);
     for (void* p : h->owned) cudaFree(p);
     for (auto& b : h->slot) b.release();
     h->st_buf.release(); h->carry_buf.release(); h->pend_buf.release(); h->csgn_buf.release();
@@ -1576,6 +1596,95 @@ dtl_status rx_host_pipelined(dtl_b200* h, int in_kind, const float* in, const fl
 
 } // namespace
 
+namespace {
+// Returns true when the call was served by the graph (status in *st); false: the caller runs the ordinary path.
+bool rx_one_frame_graph(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
+                        dtl_frame_result* res, uint8_t* bytes, int bytes_cap, int* nbytes, dtl_tb_result* tbs, int tb_cap, int* ntbs,
+                        int* frame_crc, dtl_status* st)
+{
+    static int off = -1;                             // DTL_NO_GRAPH=1: always the ordinary launches (A/B)
+    if (off < 0) { const char* e = getenv("DTL_NO_GRAPH"); off = e && atoi(e) ? 1 : 0; }
+    RxGraph& g = h->rxg;
+    if (off || g.failed || h->prof.on) return false;
+    const int mask = (res ? 1 : 0) | (bytes ? 2 : 0) | (nbytes ? 4 : 0) | (tbs ? 8 : 0) | (ntbs ? 16 : 0) | (frame_crc ? 32 : 0);
+    if (g.in_kind != in_kind || g.bytes_cap != bytes_cap || g.tb_cap != tb_cap || g.mask != mask || (g.exec && g.gen != g_alloc_gen)) {
+        g.drop();
+        g.in_kind = in_kind; g.bytes_cap = bytes_cap; g.tb_cap = tb_cap; g.mask = mask;
+    }
+    if (!g.exec && g.warm < 2) { g.warm++; return false; }          // two ordinary calls first: every buffer has its final size
+    const size_t in_bytes = (in_kind == 0 ? (size_t)h->frame_samples : (size_t)h->L * h->N) * sizeof(float2);
+    const size_t taps_bytes = (size_t)h->N * sizeof(float2);
+    auto up = [](size_t x) { return (x + 63) & ~(size_t)63; };
+    if (!g.exec) {
+        g.o_in = 0; g.o_taps = up(in_bytes); g.o_meta = g.o_taps + up(taps_bytes); g.o_res = g.o_meta + 64;
+        g.o_bytes = g.o_res + 64; g.o_nb = g.o_bytes + up((size_t)std::max(bytes_cap, 1)); g.o_tbs = g.o_nb + 64;
+        g.o_nt = g.o_tbs + up((size_t)std::max(tb_cap, 1) * sizeof(dtl_tb_result)); g.o_fcrc = g.o_nt + 64;
+        const size_t need = g.o_fcrc + 64;
+        if (need > g.pin_bytes) {
+            if (g.pin) cudaFreeHost(g.pin);
+            g.pin = nullptr; g.pin_bytes = 0;
+            if (cudaHostAlloc((void**)&g.pin, need, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); g.failed = true; return false; }
+            g.pin_bytes = need;
+        }
+        // ---- capture the ordinary code path with the page-locked buffers in the caller's place
+        cudaStreamSynchronize(h->stream);
+        if (h->side_stream) cudaStreamSynchronize(h->side_stream);
+        const unsigned long long gen0 = g_alloc_gen;
+        const uint64_t l0 = h->launches;
+        cudaGraph_t graph = nullptr;
+        bool ok = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+        if (ok) {
+            Stage sg(h, DTL_MEM_HOST);
+            const float2* d_in = sg.in(in_kind == 0 ? SL_IQ : SL_FREQ_IN, (const float2*)(g.pin + g.o_in), in_bytes / sizeof(float2));
+            const float2* d_taps = sg.in(SL_TAPS, (const float2*)(g.pin + g.o_taps), (size_t)h->N);
+            const dtl_frame_meta* d_meta = sg.in(SL_META, (const dtl_frame_meta*)(g.pin + g.o_meta), 1);
+            dtl_frame_result* d_res = res ? sg.out(SL_RES, (dtl_frame_result*)(g.pin + g.o_res), 1) : nullptr;
+            uint8_t* d_bytes = bytes ? sg.out(SL_BYTES, (uint8_t*)(g.pin + g.o_bytes), (size_t)bytes_cap) : nullptr;
+            int* d_nb = nbytes ? sg.out(SL_NBYTES, (int*)(g.pin + g.o_nb), 1) : nullptr;
+            dtl_tb_result* d_tbs = tbs ? sg.out(SL_TBS_OUT, (dtl_tb_result*)(g.pin + g.o_tbs), (size_t)tb_cap) : nullptr;
+            int* d_nt = ntbs ? sg.out(SL_NTBS, (int*)(g.pin + g.o_nt), 1) : nullptr;
+            int* d_fcrc = frame_crc ? sg.out(SL_FCRC, (int*)(g.pin + g.o_fcrc), 1) : nullptr;
+            ok = sg.e == cudaSuccess &&
+                 rx_device(h, sg, in_kind, d_in, d_taps, d_meta, 1, 1, d_res, d_bytes, bytes_cap, d_nb, d_tbs, tb_cap, d_nt, d_fcrc) == DTL_OK;
+            if (ok) ok = side_join(h) == cudaSuccess;
+            for (auto& o : sg.outs)
+                if (ok) ok = cudaMemcpyAsync(o.user, o.dev, o.bytes, cudaMemcpyDeviceToHost, h->stream) == cudaSuccess;
+            if (ok) ok = cudaMemcpyAsync(h->h_err, h->d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream) == cudaSuccess;
+            const cudaError_t ee = cudaStreamEndCapture(h->stream, &graph);
+            ok = ok && ee == cudaSuccess && graph != nullptr && gen0 == g_alloc_gen;
+        }
+        if (ok) ok = cudaGraphInstantiate(&g.exec, graph, 0) == cudaSuccess;
+        if (graph) cudaGraphDestroy(graph);
+        g.launches = h->launches - l0;
+        h->launches = l0;
+        if (!ok) {                                   // nothing ran: the ordinary path serves this call and every later one
+            cudaGetLastError();
+            h->side_pending = false; h->hdr_pending = false;
+            if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+            g.failed = true;
+            return false;
+        }
+        g.gen = g_alloc_gen;
+    }
+    // ---- replay
+    memcpy(g.pin + g.o_in, in, in_bytes);
+    memcpy(g.pin + g.o_taps, taps, taps_bytes);
+    memcpy(g.pin + g.o_meta, meta, sizeof(dtl_frame_meta));
+    cudaError_t e = cudaGraphLaunch(g.exec, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) { *st = cuda_fail(h, e, "cudaGraphLaunch"); return true; }
+    h->launches += g.launches;
+    if (res) memcpy(res, g.pin + g.o_res, sizeof(dtl_frame_result));
+    if (bytes) memcpy(bytes, g.pin + g.o_bytes, (size_t)bytes_cap);
+    if (nbytes) memcpy(nbytes, g.pin + g.o_nb, sizeof(int));
+    if (tbs) memcpy(tbs, g.pin + g.o_tbs, (size_t)tb_cap * sizeof(dtl_tb_result));
+    if (ntbs) memcpy(ntbs, g.pin + g.o_nt, sizeof(int));
+    if (frame_crc) memcpy(frame_crc, g.pin + g.o_fcrc, sizeof(int));
+    *st = check_device_error(h);
+    return true;
+}
+} // namespace
+
 extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, const float* taps, const dtl_frame_meta* meta,
                                   int32_t n_streams, int32_t frames_per_stream, dtl_frame_result* res,
                                   uint8_t* bytes, int32_t bytes_cap, int32_t* nbytes,
@@ -1589,6 +1698,8 @@ extern "C" dtl_status dtl_b200_rx(dtl_b200* h, int in_kind, const float* in, con
     dtl_status s = check_meta_host(h, meta, (long long)n, mem);
     if (s != DTL_OK) return s;
     if ((s = ensure_streams(h, S)) != DTL_OK) return s;
+    if (mem == DTL_MEM_HOST && S == 1 && F == 1 &&
+        rx_one_frame_graph(h, in_kind, in, taps, meta, res, bytes, bytes_cap, nbytes, tbs, tb_cap, ntbs, frame_crc, &s)) return s;
     if (mem == DTL_MEM_HOST && F > 0) {
         // chunks of about 48 MB of input, at least 4 of them
         const size_t per_stream = (size_t)F * (in_kind == 0 ? (size_t)h->frame_samples : LN) * sizeof(float2);

@@ -33,6 +33,7 @@
 #include "kernels.cuh"
 #include "bp_ref.cuh"
 #include "bp_layered.cuh"
+#include <algorithm>
 #include <cstdlib>
 
 namespace dtl {
@@ -1352,12 +1353,15 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         prof->begin(DTL_STAGE_LDPC, 2);
         static int per_sm_screen = 0;                // CTAs per SM of the grid-stride screening pass (6 are resident at 40 registers)
         if (!per_sm_screen) { const char* e = getenv("DTL_SCREEN_CTAS"); per_sm_screen = e && atoi(e) > 0 ? atoi(e) : 8; }
-        ldpc_screen_kernel<<<sm_count * per_sm_screen, 256, smem, st>>>(p);
+        // a call with little work (the one-frame latency mode) does not launch -- and stage tables in -- a full machine's CTAs
+        const long long scr_need = ((long long)p.cw_cap + 255) / 256;               // 32 codewords per warp, 8 warps per CTA
+        const int scr_grid = (int)std::max(1ll, std::min((long long)sm_count * per_sm_screen, scr_need));
+        ldpc_screen_kernel<<<scr_grid, 256, smem, st>>>(p);
     }
     if (p.fast) {   // pass 2, reference mode on codes with a row-major instance (bp_ref.cuh)
         static int wsel = 0;                         // DTL_BP_TEAM=32|64: threads per codeword (A/B; 64 = two warps per codeword)
         if (!wsel) { const char* e = getenv("DTL_BP_TEAM"); wsel = e && atoi(e) > 0 ? atoi(e) : 32; }
-        bp_gather_kernel<<<sm_count * 8, 256, 0, st>>>(p);
+        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 7) / 8)), 256, 0, st>>>(p);
         const size_t per_warp = (size_t)p.fast_warp_bytes + (size_t)p.cw_stride * 4;
         auto launch = [&](auto kern, int teams, int threads, int max_ctas) {
             const size_t sm_bytes = (size_t)p.fast_tab_bytes + per_warp * teams;
@@ -1365,7 +1369,8 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
             if (per_sm < 1) per_sm = 1;
             if (per_sm > max_ctas) per_sm = max_ctas;
             if (sm_bytes + 256 > 227 * 1024) return cudaErrorInvalidConfiguration;
-            kern<<<sm_count * per_sm, threads, sm_bytes, st>>>(p);
+            const long long need = ((long long)p.cw_cap + teams - 1) / teams;
+            kern<<<(int)std::max(1ll, std::min((long long)sm_count * per_sm, need)), threads, sm_bytes, st>>>(p);
             return cudaSuccess;
         };
         // One CTA of 19 warps per SM where 19 codewords fit (n = 300: 221 KB) -- the code tables are staged once per SM instead of
@@ -1380,14 +1385,14 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         if (launches) *launches += 1;
         prof->end();
     } else if (p.lay) {   // pass 2, layered mode on codes with row-major tables (bp_layered.cuh)
-        bp_gather_kernel<<<sm_count * 8, 256, 0, st>>>(p);
+        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 7) / 8)), 256, 0, st>>>(p);
         const int W = 8;
         const size_t sm_bytes = (size_t)p.lay_tab_bytes + ((size_t)p.lay_warp_bytes + (size_t)p.cw_stride * 4) * W;
         if (sm_bytes + 256 > 227 * 1024) return cudaErrorInvalidConfiguration;
         int per_sm = (int)((227 * 1024) / (sm_bytes + 1024 + 256));
         if (per_sm < 1) per_sm = 1;
         if (per_sm > 4) per_sm = 4;                  // 64 registers per thread: four CTAs of eight warps (5 / 6 CTAs at 48 / 40 registers measured 4 % slower)
-        ldpc_bp_lay_kernel<8, 4><<<sm_count * per_sm, W * 32, sm_bytes, st>>>(p);
+        ldpc_bp_lay_kernel<8, 4><<<(int)std::max(1ll, std::min((long long)sm_count * per_sm, ((long long)p.cw_cap + W - 1) / W)), W * 32, sm_bytes, st>>>(p);
         if (launches) *launches += 1;
         prof->end();
     } else {   // pass 2: belief propagation on what did not pass, persistent
