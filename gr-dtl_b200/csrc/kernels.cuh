@@ -86,7 +86,11 @@ struct StreamParams {
     int n_mcs; const double* mcs_snr; const int* mcs_cnst; const int* mcs_fec; double hysteresis; int decision_th;
 };
 
-struct BpItem { long long out_off; int it, fec_id, k_, pad; };   // where a queued codeword's bits go (bp_gather_kernel -> ldpc_bp_ref_kernel)
+// One queued codeword (bp_gather_kernel -> ldpc_bp_ref_kernel / ldpc_bp_lay_kernel): where its bits go, and what the decoder's
+// bulk copy fetches -- `nbytes` (a multiple of 16) from `src` (16-byte aligned: the LLR row itself, or the codeword's gathered
+// block in cwbuf); wire position q of the codeword is float shift + q of the copy for q < len, a shortened position past it.
+struct BpItem { long long out_off; const float* src; int it, fec_id, k_, shift, nbytes, len; };
+#define DTL_STG_SLACK 32                             // bytes a staging block has beyond cw_stride floats: lead-in + round-up of an unaligned run
 
 // ---- stage 4 ------------------------------------------------------------------------------------------------
 struct FecParams {

@@ -859,43 +859,82 @@ __device__ __forceinline__ double lr_of_rx(float x, double sigma2, const double2
 // one before it (profiles/r02a: a third of the decoder's warps sat in that chain at any time).
 __global__ void __launch_bounds__(256) bp_gather_kernel(FecParams p)
 {
-    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    __shared__ int s_list[256];
+    __shared__ int s_n;
+    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5, wid = threadIdx.x >> 5;
     const int n0 = p.cnt[3], n1 = n0 + p.cnt[5], n2 = n1 + p.cnt[6], total = n2 + p.cnt[7];
-    for (int j = blockIdx.x * warps + (threadIdx.x >> 5); j < total; j += gridDim.x * warps) {
-        const int it = j < n0 ? p.bp_list[j] : j < n1 ? p.bp_list[(size_t)p.cw_cap + (j - n0)]
-                     : j < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (j - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (j - n2)];
-        const TbDesc& d = p.tbs[p.cw_tb[it]];
-        const CodeDev& c = p.codes[d.fec_id];
-        const int n = c.n, rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - c.k) + k_;
-        float* dst = p.cwbuf + (size_t)j * p.cw_stride;
-        if (lane == 0) {
+    for (int j0 = blockIdx.x * blockDim.x; j0 < total; j0 += gridDim.x * blockDim.x) {
+        if (threadIdx.x == 0) s_n = 0;
+        __syncthreads();
+        // one THREAD per queued codeword: a codeword whose received run lies inside one segment (one frame's LLR row, or the
+        // carry buffer) is not copied at all -- its record points the decoder's bulk copy at the 16-byte-aligned superset of
+        // the run (`shift` floats of lead-in) as long as that superset stays inside the row; the others go to the list below
+        const int j = j0 + threadIdx.x;
+        if (j < total) {
+            const int it = j < n0 ? p.bp_list[j] : j < n1 ? p.bp_list[(size_t)p.cw_cap + (j - n0)]
+                         : j < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (j - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (j - n2)];
+            const TbDesc& d = p.tbs[p.cw_tb[it]];
+            const CodeDev& c = p.codes[d.fec_id];
+            const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (c.n - c.k) + k_;
             BpItem r;
-            r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_; r.pad = 0;
-            p.items[j] = r;
-        }
-        // wire order, coalesced: defaults first (positions past the received length read as LLR 0, shortened ones as -15), then
-        // every segment that overlaps the codeword copies its run; the column permutation is applied by the decoder when it
-        // turns the block into likelihood ratios (a shared-memory scatter there, a sector-wasting global one here)
-        for (int q = lane; q < p.cw_stride; q += 32) dst[q] = q < len ? -0.0f : 15.0f;      // -1 * 0 and -1 * -15
-        __syncwarp();
-        const int nseg = d.nseg;
-        int base = 0;
-        for (int i = 0; i < nseg; i++) {
-            const TbSeg sg = d.seg[i];
-            const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
-            if (lo < hi) {
-                const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
-                                              : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
-                for (int g0 = lo + lane; g0 < hi; g0 += 320) {           // ten loads per lane in flight: a whole n <= 320 codeword
-                    float xv[10];
-#pragma unroll
-                    for (int u = 0; u < 10; u++) { const int g = g0 + 32 * u; xv[u] = g < hi ? __ldcs(&src[g - base]) : 0.f; }
-#pragma unroll
-                    for (int u = 0; u < 10; u++) { const int g = g0 + 32 * u; if (g < hi) dst[g - rcv_idx] = -1 * xv[u]; }
+            r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_;
+            r.src = nullptr; r.shift = 0; r.nbytes = 0; r.len = len;
+            const int nseg = d.nseg;
+            int base = 0;
+            for (int i = 0; i < nseg; i++) {
+                const TbSeg sg = d.seg[i];
+                if (rcv_idx >= base && rcv_idx + len <= base + sg.len) {
+                    const float* row = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap
+                                                  : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride;
+                    const size_t row_bytes = (size_t)(sg.src < 0 ? p.carry_cap : p.llr_stride) * 4;
+                    const uintptr_t a = (uintptr_t)(row + sg.start + (rcv_idx - base));
+                    const uintptr_t a0 = a & ~(uintptr_t)15, a1 = (a + (size_t)len * 4 + 15) & ~(uintptr_t)15;
+                    if (a0 >= (uintptr_t)row && a1 <= (uintptr_t)row + row_bytes) {
+                        r.src = (const float*)a0; r.shift = (int)((a - a0) >> 2); r.nbytes = (int)(a1 - a0);
+                    }
+                    break;
                 }
+                base += sg.len;
             }
-            base += sg.len;
+            if (r.src) p.items[j] = r;
+            else s_list[atomicAdd(&s_n, 1)] = j;
         }
+        __syncthreads();
+        // the rest (runs that straddle two frames, TBs cut short): one WARP per codeword copies the pieces into its block of
+        // cwbuf, wire order, coalesced: defaults first (positions past the received length read as LLR 0, shortened ones as
+        // -15), then every segment that overlaps the codeword copies its run.  Values as received: the decoder negates
+        // (ldpc_dec.cc:64) and applies the column permutation when it consumes the block
+        const int nl = s_n;
+        for (int li = wid; li < nl; li += warps) {
+            const int jj = s_list[li];
+            const int it = jj < n0 ? p.bp_list[jj] : jj < n1 ? p.bp_list[(size_t)p.cw_cap + (jj - n0)]
+                         : jj < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (jj - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (jj - n2)];
+            const TbDesc& d = p.tbs[p.cw_tb[it]];
+            const CodeDev& c = p.codes[d.fec_id];
+            const int n = c.n, rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - c.k) + k_;
+            float* dst = p.cwbuf + (size_t)jj * p.cw_stride;
+            if (lane == 0) {
+                BpItem r;
+                r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_;
+                r.src = dst; r.shift = 0; r.nbytes = p.cw_stride * 4; r.len = n;
+                p.items[jj] = r;
+            }
+            for (int q = lane; q < p.cw_stride; q += 32) dst[q] = q < len ? 0.0f : -15.0f;
+            __syncwarp();
+            const int nseg = d.nseg;
+            int base = 0;
+            for (int i = 0; i < nseg; i++) {
+                const TbSeg sg = d.seg[i];
+                const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+                if (lo < hi) {
+                    const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                                  : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                    for (int g = lo + lane; g < hi; g += 32) dst[g - rcv_idx] = __ldcs(&src[g - base]);
+                }
+                base += sg.len;
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -938,17 +977,17 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
         if (tid == 0) { mbar_init(&bars[team], 1); s_next[team] = atomicAdd(&p.cnt[1], 1); }
         __syncthreads();
     }
-    const int stg_bytes = p.cw_stride * 4;
+    const int stg_bytes = p.cw_stride * 4 + DTL_STG_SLACK;
     unsigned char* base = sm + p.fast_tab_bytes + (size_t)team * (p.fast_warp_bytes + stg_bytes);
     float* stg = (float*)(base + p.fast_warp_bytes);
     uint64_t* bar = &bars[team];
     const int total = p.cnt[3] + p.cnt[5] + p.cnt[6] + p.cnt[7];
     int j = s_next[team];
     BpItem rec;
-    rec.out_off = 0; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.pad = 0;
+    rec.out_off = 0; rec.src = nullptr; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.shift = 0; rec.nbytes = 0; rec.len = 0;
     if (j < total) {
-        if (tid == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)j * p.cw_stride, (uint32_t)stg_bytes, bar); }
         rec = p.items[j];
+        if (tid == 0) { mbar_expect_tx(bar, (uint32_t)rec.nbytes); bulk_g2s(stg, rec.src, (uint32_t)rec.nbytes, bar); }
     }
     team_sync<NT>(bar_id);                                             // everybody has read s_next
     uint32_t phase = 0;
@@ -960,7 +999,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
         mbar_wait(bar, phase);
         phase ^= 1u;
         for (int q = tid; q < c.n; q += NT) {                          // ldpc_dec.cc:64-66, rx_lr_calc, compute_init_estimate
-            const float x = stg[q];
+            const float x = q < rec.len ? -1 * stg[rec.shift + q] : 15.0f;      // shortened positions: -1 * -15
             const int col = c.permute()[q];
             w.lr0[col] = lr_of_rx(x, p.sigma2_lr, p.exp_tab);
             w.est[col] = x < 0.f ? 1 : 0;
@@ -969,8 +1008,8 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
         const int nxt = s_next[team];
         BpItem nrec = rec;
         if (nxt < total) {
-            if (tid == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)nxt * p.cw_stride, (uint32_t)stg_bytes, bar); }
             nrec = p.items[nxt];
+            if (tid == 0) { mbar_expect_tx(bar, (uint32_t)nrec.nbytes); bulk_g2s(stg, nrec.src, (uint32_t)nrec.nbytes, bar); }
         }
         const int nit = NT == 32 ? bp_ref_run<NT>(c, w, tid, p.max_it, bar_id) : bp_ref_call<NT>(&scodes[rec.fec_id], base, sm, tid, p.max_it, bar_id);
         uint8_t* out = p.bits + rec.out_off;
@@ -1001,7 +1040,7 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
         if (lane == 0) mbar_init(&bars[wid], 1);
         __syncthreads();
     }
-    const int stg_bytes = p.cw_stride * 4;
+    const int stg_bytes = p.cw_stride * 4 + DTL_STG_SLACK;
     unsigned char* base = sm + p.lay_tab_bytes + (size_t)wid * (p.lay_warp_bytes + stg_bytes);
     float* stg = (float*)(base + p.lay_warp_bytes);
     uint64_t* bar = &bars[wid];
@@ -1010,10 +1049,10 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
     if (lane == 0) j = atomicAdd(&p.cnt[1], 1);
     j = __shfl_sync(0xffffffffu, j, 0);
     BpItem rec;
-    rec.out_off = 0; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.pad = 0;
+    rec.out_off = 0; rec.src = nullptr; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.shift = 0; rec.nbytes = 0; rec.len = 0;
     if (j < total) {
-        if (lane == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)j * p.cw_stride, (uint32_t)stg_bytes, bar); }
         rec = p.items[j];
+        if (lane == 0) { mbar_expect_tx(bar, (uint32_t)rec.nbytes); bulk_g2s(stg, rec.src, (uint32_t)rec.nbytes, bar); }
     }
     uint32_t phase = 0;
     while (j < total) {
@@ -1025,13 +1064,13 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
         mbar_wait(bar, phase);
         phase ^= 1u;
         if (lane == 0) w.post[c.ns] = 1.0e30f;                                      // pad edge of the lighter rows
-        for (int q = lane; q < c.n; q += 32) w.post[c.permute()[q]] = stg[q];       // ldpc_dec.cc:64-66 (the block holds -llr)
+        for (int q = lane; q < c.n; q += 32) w.post[c.permute()[q]] = q < rec.len ? -1 * stg[rec.shift + q] : 15.0f;   // ldpc_dec.cc:64-66
         __syncwarp();
         nxt = __shfl_sync(0xffffffffu, nxt, 0);
         BpItem nrec = rec;
         if (nxt < total) {
-            if (lane == 0) { mbar_expect_tx(bar, (uint32_t)stg_bytes); bulk_g2s(stg, p.cwbuf + (size_t)nxt * p.cw_stride, (uint32_t)stg_bytes, bar); }
             nrec = p.items[nxt];
+            if (lane == 0) { mbar_expect_tx(bar, (uint32_t)nrec.nbytes); bulk_g2s(stg, nrec.src, (uint32_t)nrec.nbytes, bar); }
         }
         const int nit = bp_lay_run(c, w, lane, p.max_it);
         uint8_t* out = p.bits + rec.out_off;
@@ -1361,8 +1400,8 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
     if (p.fast) {   // pass 2, reference mode on codes with a row-major instance (bp_ref.cuh)
         static int wsel = 0;                         // DTL_BP_TEAM=32|64: threads per codeword (A/B; 64 = two warps per codeword)
         if (!wsel) { const char* e = getenv("DTL_BP_TEAM"); wsel = e && atoi(e) > 0 ? atoi(e) : 32; }
-        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 7) / 8)), 256, 0, st>>>(p);
-        const size_t per_warp = (size_t)p.fast_warp_bytes + (size_t)p.cw_stride * 4;
+        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 255) / 256)), 256, 0, st>>>(p);
+        const size_t per_warp = (size_t)p.fast_warp_bytes + (size_t)p.cw_stride * 4 + DTL_STG_SLACK;
         auto launch = [&](auto kern, int teams, int threads, int max_ctas) {
             const size_t sm_bytes = (size_t)p.fast_tab_bytes + per_warp * teams;
             int per_sm = (int)((227 * 1024) / (sm_bytes + 1024 + 256));
@@ -1385,9 +1424,9 @@ cudaError_t launch_fec(cudaStream_t st, const FecParams& p, int sm_count, int* l
         if (launches) *launches += 1;
         prof->end();
     } else if (p.lay) {   // pass 2, layered mode on codes with row-major tables (bp_layered.cuh)
-        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 7) / 8)), 256, 0, st>>>(p);
+        bp_gather_kernel<<<(int)std::max(1ll, std::min((long long)sm_count * 8, ((long long)p.cw_cap + 255) / 256)), 256, 0, st>>>(p);
         const int W = 8;
-        const size_t sm_bytes = (size_t)p.lay_tab_bytes + ((size_t)p.lay_warp_bytes + (size_t)p.cw_stride * 4) * W;
+        const size_t sm_bytes = (size_t)p.lay_tab_bytes + ((size_t)p.lay_warp_bytes + (size_t)p.cw_stride * 4 + DTL_STG_SLACK) * W;
         if (sm_bytes + 256 > 227 * 1024) return cudaErrorInvalidConfiguration;
         int per_sm = (int)((227 * 1024) / (sm_bytes + 1024 + 256));
         if (per_sm < 1) per_sm = 1;
