@@ -992,7 +992,10 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
     team_sync<NT>(bar_id);                                             // everybody has read s_next
     uint32_t phase = 0;
     while (j < total) {
-        if (tid == 0) s_next[team] = atomicAdd(&p.cnt[1], 1);         // its latency hides behind the likelihood-ratio pass
+        // the claim of the next codeword: issued here, first looked at after the likelihood-ratio pass (one warp per codeword:
+        // through a shuffle, not through shared memory -- a store of the atomic's result would wait for it right here)
+        int nx = 0;
+        if (tid == 0) { nx = atomicAdd(&p.cnt[1], 1); if (NT != 32) s_next[team] = nx; }
         FastS c = scodes[rec.fec_id];
         c.smb = sm;
         const FastBuf w = fast_carve(base, c.n, c.m, c.rs);
@@ -1005,7 +1008,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
             w.est[col] = x < 0.f ? 1 : 0;
         }
         team_sync<NT>(bar_id);
-        const int nxt = s_next[team];
+        const int nxt = NT == 32 ? __shfl_sync(0xffffffffu, nx, 0) : s_next[team];
         BpItem nrec = rec;
         if (nxt < total) {
             nrec = p.items[nxt];
