@@ -43,7 +43,7 @@ enum Slot {
     SL_FCRC, SL_FREQ, SL_BYTES, SL_NBYTES, SL_TBS_OUT, SL_NTBS, SL_NOISE, SL_SYMS, SL_CHUNKS, SL_BITS_OUT, SL_NIT,
     SL_HDR, SL_TXIQ, SL_FFT_IN, SL_FFT_OUT, SL_ENC_IN, SL_ENC_OUT,
     // FEC scratch
-    SL_CWBUF, SL_BPITEMS, SL_SGN, SL_SYX, SL_SYFLAGS, SL_SYSEGS, SL_SYNSEG, SL_SYRAW, SL_SYFIXED, SL_SYSTARTS, SL_SYSTARTS_OUT, SL_SYNFR, SL_SYFRAMES, SL_SYVALID, SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
+    SL_CWBUF, SL_BPITEMS, SL_GLIST, SL_SGN, SL_SYX, SL_SYFLAGS, SL_SYSEGS, SL_SYNSEG, SL_SYRAW, SL_SYFIXED, SL_SYSTARTS, SL_SYSTARTS_OUT, SL_SYNFR, SL_SYFRAMES, SL_SYVALID, SL_TBDESC, SL_TRES, SL_TBCOUNT, SL_TBLIST, SL_CWTB, SL_CWNIT, SL_CWGEO, SL_BPLIST, SL_BITS, SL_MAG, SL_HFREQ, SL_HMETA, SL_HTAPS, SL_HRES,
     SL_TXDATA, SL_TXLEN, SL_TXCNST, SL_TXFEC, SL_TXTBS, SL_TXNTB, SL_TXKEEP, SL_TXSEGS, SL_TXCRC, SL_TXBITS, SL_TXCHUNKS, SL_TXMETA, SL_TXCONS, SL_TXSTARTED, SL_COUNT
 };
 
@@ -1182,7 +1182,8 @@ dtl_status fec_prepare(dtl_b200* h, Stage& sg, const float* llr, int llr_stride,
     if (p.fast || p.lay) {
         p.cw_stride = (h->max_n + 3) & ~3;           // 16-byte multiples: one bulk copy per codeword
         p.cwbuf = sg.scratch<float>(SL_CWBUF, (size_t)p.cw_cap * p.cw_stride);
-        p.items = sg.scratch<BpItem>(SL_BPITEMS, (size_t)p.cw_cap);
+        p.items = sg.scratch<BpItem>(SL_BPITEMS, 4 * (size_t)p.cw_cap);
+        p.glist = sg.scratch<int>(SL_GLIST, (size_t)p.cw_cap);
         if (sg.e != cudaSuccess) return cuda_fail(h, sg.e, "FEC scratch");
     }
     p.bytes = bytes; p.bytes_cap = bytes_cap; p.nbytes = nbytes; p.tb_out = tbs; p.tb_cap = tb_cap; p.ntbs = ntbs;

@@ -109,7 +109,7 @@ struct FecParams {
     int* tb_count;                                 // [S]
     int* tb_list;                                  // compact list of released TB indices
     int* cw_tb; int cw_cap;                        // codeword work list: TB index of work item
-    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs, [3],[5],[6],[7] queued for BP
+    int* cnt;                                      // [0] codewords, [1] work cursor, [2] released TBs, [3],[5],[6],[7] queued for BP, [10] of them to be gathered
     unsigned long long* bits_used;                 // bump allocator of the bit scratch
     uint8_t* bits; long long bits_cap;             // decoded TB bits, one byte per bit, then packed in place
     int* cw_nit;                                   // [cw_cap]
@@ -125,7 +125,8 @@ struct FecParams {
     int lay; int lay_tab_bytes, lay_warp_bytes;    // layered mode on codes with row-major tables: ldpc_bp_lay_kernel
     double sigma2_lr;                              // sigma2, or -(1/sigma2) when sigma2 is a power of two (lr_of_rx)
     float* cwbuf; int cw_stride;                   // [queued codewords][cw_stride] received values in H column order (bp_gather_kernel)
-    BpItem* items;                                 // [queued codewords]
+    BpItem* items;                                 // [4][cw_cap] records of the queued codewords, same positions as bp_list (ldpc_screen_kernel)
+    int* glist;                                    // [cnt[10]] positions of the queued codewords whose runs bp_gather_kernel copies into cwbuf
     // outputs
     uint8_t* bytes; int bytes_cap; int* nbytes; dtl_tb_result* tb_out; int tb_cap; int* ntbs;
     const uint32_t* crc_table; int* err;

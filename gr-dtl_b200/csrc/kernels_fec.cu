@@ -583,6 +583,44 @@ __device__ __forceinline__ unsigned transpose32(unsigned x, int lane)
     return x;
 }
 
+// The record of a codeword the screening pass queues for belief propagation (BpItem), written at queue position `pos` (class *
+// cw_cap + rank in the class).  A codeword whose received run lies inside one segment (one frame's LLR row, or the carry buffer)
+// is not copied at all: the record points the decoder's bulk copy at the 16-byte-aligned superset of the run (`shift` floats of
+// lead-in) as long as that superset stays inside the row.  The others (runs that straddle two frames, TBs cut short) take a
+// block of cwbuf, which bp_gather_kernel fills.
+__device__ __forceinline__ void bp_make_item(const FecParams& p, int it, size_t pos)
+{
+    const TbDesc& d = p.tbs[p.cw_tb[it]];
+    const CodeDev& c = p.codes[d.fec_id];
+    const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (c.n - c.k) + k_;
+    BpItem r;
+    r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_;
+    r.src = nullptr; r.shift = 0; r.nbytes = 0; r.len = len;
+    const int nseg = d.nseg;
+    int base = 0;
+    for (int i = 0; i < nseg; i++) {
+        const TbSeg sg = d.seg[i];
+        if (rcv_idx >= base && rcv_idx + len <= base + sg.len) {
+            const float* row = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap
+                                          : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride;
+            const size_t row_bytes = (size_t)(sg.src < 0 ? p.carry_cap : p.llr_stride) * 4;
+            const uintptr_t a = (uintptr_t)(row + sg.start + (rcv_idx - base));
+            const uintptr_t a0 = a & ~(uintptr_t)15, a1 = (a + (size_t)len * 4 + 15) & ~(uintptr_t)15;
+            if (a0 >= (uintptr_t)row && a1 <= (uintptr_t)row + row_bytes) {
+                r.src = (const float*)a0; r.shift = (int)((a - a0) >> 2); r.nbytes = (int)(a1 - a0);
+            }
+            break;
+        }
+        base += sg.len;
+    }
+    if (!r.src) {
+        const int g = atomicAdd(&p.cnt[10], 1);
+        p.glist[g] = (int)pos;
+        r.src = p.cwbuf + (size_t)g * p.cw_stride; r.nbytes = p.cw_stride * 4; r.len = c.n;
+    }
+    p.items[pos] = r;
+}
+
 #ifndef DTL_SCREEN_UNROLL
 #define DTL_SCREEN_UNROLL 5      // loads in flight per lane (A/B: 4 -> 2.143 ms LDPC stage, 5 -> 2.090, 10 -> 2.099)
 #endif
@@ -790,7 +828,11 @@ __global__ void __launch_bounds__(256) ldpc_screen_kernel(FecParams p)
                 int base = 0;
                 if (lane == 0) base = atomicAdd(&p.cnt[b == 0 ? 3 : 4 + b], __popc(mk));
                 base = __shfl_sync(0xffffffffu, base, 0);
-                if ((mk >> lane) & 1u) p.bp_list[(size_t)b * p.cw_cap + base + __popc(mk & ((1u << lane) - 1u))] = it0 + lane;
+                if ((mk >> lane) & 1u) {
+                    const size_t pos = (size_t)b * p.cw_cap + base + __popc(mk & ((1u << lane) - 1u));
+                    p.bp_list[pos] = it0 + lane;
+                    if (p.items) bp_make_item(p, it0 + lane, pos);
+                }
             }
         }
         __syncwarp();
@@ -859,82 +901,32 @@ __device__ __forceinline__ double lr_of_rx(float x, double sigma2, const double2
 // one before it (profiles/r02a: a third of the decoder's warps sat in that chain at any time).
 __global__ void __launch_bounds__(256) bp_gather_kernel(FecParams p)
 {
-    __shared__ int s_list[256];
-    __shared__ int s_n;
-    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5, wid = threadIdx.x >> 5;
-    const int n0 = p.cnt[3], n1 = n0 + p.cnt[5], n2 = n1 + p.cnt[6], total = n2 + p.cnt[7];
-    for (int j0 = blockIdx.x * blockDim.x; j0 < total; j0 += gridDim.x * blockDim.x) {
-        if (threadIdx.x == 0) s_n = 0;
-        __syncthreads();
-        // one THREAD per queued codeword: a codeword whose received run lies inside one segment (one frame's LLR row, or the
-        // carry buffer) is not copied at all -- its record points the decoder's bulk copy at the 16-byte-aligned superset of
-        // the run (`shift` floats of lead-in) as long as that superset stays inside the row; the others go to the list below
-        const int j = j0 + threadIdx.x;
-        if (j < total) {
-            const int it = j < n0 ? p.bp_list[j] : j < n1 ? p.bp_list[(size_t)p.cw_cap + (j - n0)]
-                         : j < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (j - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (j - n2)];
-            const TbDesc& d = p.tbs[p.cw_tb[it]];
-            const CodeDev& c = p.codes[d.fec_id];
-            const int rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (c.n - c.k) + k_;
-            BpItem r;
-            r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_;
-            r.src = nullptr; r.shift = 0; r.nbytes = 0; r.len = len;
-            const int nseg = d.nseg;
-            int base = 0;
-            for (int i = 0; i < nseg; i++) {
-                const TbSeg sg = d.seg[i];
-                if (rcv_idx >= base && rcv_idx + len <= base + sg.len) {
-                    const float* row = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap
-                                                  : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride;
-                    const size_t row_bytes = (size_t)(sg.src < 0 ? p.carry_cap : p.llr_stride) * 4;
-                    const uintptr_t a = (uintptr_t)(row + sg.start + (rcv_idx - base));
-                    const uintptr_t a0 = a & ~(uintptr_t)15, a1 = (a + (size_t)len * 4 + 15) & ~(uintptr_t)15;
-                    if (a0 >= (uintptr_t)row && a1 <= (uintptr_t)row + row_bytes) {
-                        r.src = (const float*)a0; r.shift = (int)((a - a0) >> 2); r.nbytes = (int)(a1 - a0);
-                    }
-                    break;
-                }
-                base += sg.len;
+    // one WARP per queued codeword that needs gathering (bp_make_item): the pieces go into its block of cwbuf, wire order,
+    // coalesced: defaults first (positions past the received length read as LLR 0, shortened ones as -15), then every segment
+    // that overlaps the codeword copies its run.  Values as received: the decoder negates (ldpc_dec.cc:64) and applies the
+    // column permutation when it consumes the block
+    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    const int nl = p.cnt[10];
+    for (int li = blockIdx.x * warps + (threadIdx.x >> 5); li < nl; li += gridDim.x * warps) {
+        const int it = p.bp_list[p.glist[li]];
+        const TbDesc& d = p.tbs[p.cw_tb[it]];
+        const CodeDev& c = p.codes[d.fec_id];
+        const int rcv_idx = p.cw_geo[3 * it], len = (c.n - c.k) + p.cw_geo[3 * it + 2];
+        float* dst = p.cwbuf + (size_t)li * p.cw_stride;
+        for (int q = lane; q < p.cw_stride; q += 32) dst[q] = q < len ? 0.0f : -15.0f;
+        __syncwarp();
+        const int nseg = d.nseg;
+        int base = 0;
+        for (int i = 0; i < nseg; i++) {
+            const TbSeg sg = d.seg[i];
+            const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
+            if (lo < hi) {
+                const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
+                                              : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
+                for (int g = lo + lane; g < hi; g += 32) dst[g - rcv_idx] = __ldcs(&src[g - base]);
             }
-            if (r.src) p.items[j] = r;
-            else s_list[atomicAdd(&s_n, 1)] = j;
+            base += sg.len;
         }
-        __syncthreads();
-        // the rest (runs that straddle two frames, TBs cut short): one WARP per codeword copies the pieces into its block of
-        // cwbuf, wire order, coalesced: defaults first (positions past the received length read as LLR 0, shortened ones as
-        // -15), then every segment that overlaps the codeword copies its run.  Values as received: the decoder negates
-        // (ldpc_dec.cc:64) and applies the column permutation when it consumes the block
-        const int nl = s_n;
-        for (int li = wid; li < nl; li += warps) {
-            const int jj = s_list[li];
-            const int it = jj < n0 ? p.bp_list[jj] : jj < n1 ? p.bp_list[(size_t)p.cw_cap + (jj - n0)]
-                         : jj < n2 ? p.bp_list[2 * (size_t)p.cw_cap + (jj - n1)] : p.bp_list[3 * (size_t)p.cw_cap + (jj - n2)];
-            const TbDesc& d = p.tbs[p.cw_tb[it]];
-            const CodeDev& c = p.codes[d.fec_id];
-            const int n = c.n, rcv_idx = p.cw_geo[3 * it], k_ = p.cw_geo[3 * it + 2], len = (n - c.k) + k_;
-            float* dst = p.cwbuf + (size_t)jj * p.cw_stride;
-            if (lane == 0) {
-                BpItem r;
-                r.out_off = d.bit_base + p.cw_geo[3 * it + 1]; r.it = it; r.fec_id = d.fec_id; r.k_ = k_;
-                r.src = dst; r.shift = 0; r.nbytes = p.cw_stride * 4; r.len = n;
-                p.items[jj] = r;
-            }
-            for (int q = lane; q < p.cw_stride; q += 32) dst[q] = q < len ? 0.0f : -15.0f;
-            __syncwarp();
-            const int nseg = d.nseg;
-            int base = 0;
-            for (int i = 0; i < nseg; i++) {
-                const TbSeg sg = d.seg[i];
-                const int lo = max(rcv_idx, base), hi = min(rcv_idx + len, base + sg.len);
-                if (lo < hi) {
-                    const float* src = sg.src < 0 ? p.carry + (size_t)d.stream * p.carry_cap + sg.start
-                                                  : p.llr + ((size_t)d.stream * p.F + sg.src) * p.llr_stride + sg.start;
-                    for (int g = lo + lane; g < hi; g += 32) dst[g - rcv_idx] = __ldcs(&src[g - base]);
-                }
-                base += sg.len;
-            }
-        }
-        __syncthreads();
     }
 }
 
@@ -948,6 +940,12 @@ __device__ __noinline__ int bp_ref_call(const FastS* cp, unsigned char* base, co
     c.smb = smb;
     const FastBuf w = fast_carve(base, c.n, c.m, c.rs);
     return bp_ref_run<NT>(c, w, tid, max_it, bar_id);
+}
+
+// queue position j (hardest class first) -> index of the codeword's record: class * cw_cap + rank in the class
+__device__ __forceinline__ size_t bp_item_pos(const int* q, int j, int cap)
+{
+    return j < q[0] ? (size_t)j : j < q[1] ? (size_t)cap + (j - q[0]) : j < q[2] ? 2 * (size_t)cap + (j - q[1]) : 3 * (size_t)cap + (j - q[2]);
 }
 
 // Pass 2, reference mode: persistent, one codeword per TEAM of NT threads (NT / 32 warps behind a named barrier) from the
@@ -965,6 +963,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
     __shared__ FastS scodes[DTL_MAX_SMEM_CODES];
     __shared__ __align__(8) uint64_t bars[TEAMS];
     __shared__ int s_next[TEAMS];
+    __shared__ int s_q[3];
     const int team = threadIdx.x / NT, tid = threadIdx.x - team * NT, bar_id = team + 1;
     {
         int off = 0;
@@ -975,6 +974,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
             off += (int)fast_tab_bytes(g.n, g.m, g.nvr);
         }
         if (tid == 0) { mbar_init(&bars[team], 1); s_next[team] = atomicAdd(&p.cnt[1], 1); }
+        if (threadIdx.x == 0) { s_q[0] = p.cnt[3]; s_q[1] = s_q[0] + p.cnt[5]; s_q[2] = s_q[1] + p.cnt[6]; }
         __syncthreads();
     }
     const int stg_bytes = p.cw_stride * 4 + DTL_STG_SLACK;
@@ -986,7 +986,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
     BpItem rec;
     rec.out_off = 0; rec.src = nullptr; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.shift = 0; rec.nbytes = 0; rec.len = 0;
     if (j < total) {
-        rec = p.items[j];
+        rec = p.items[bp_item_pos(s_q, j, p.cw_cap)];
         if (tid == 0) { mbar_expect_tx(bar, (uint32_t)rec.nbytes); bulk_g2s(stg, rec.src, (uint32_t)rec.nbytes, bar); }
     }
     team_sync<NT>(bar_id);                                             // everybody has read s_next
@@ -1011,7 +1011,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
         const int nxt = NT == 32 ? __shfl_sync(0xffffffffu, nx, 0) : s_next[team];
         BpItem nrec = rec;
         if (nxt < total) {
-            nrec = p.items[nxt];
+            nrec = p.items[bp_item_pos(s_q, nxt, p.cw_cap)];
             if (tid == 0) { mbar_expect_tx(bar, (uint32_t)nrec.nbytes); bulk_g2s(stg, nrec.src, (uint32_t)nrec.nbytes, bar); }
         }
         const int nit = NT == 32 ? bp_ref_run<NT>(c, w, tid, p.max_it, bar_id) : bp_ref_call<NT>(&scodes[rec.fec_id], base, sm, tid, p.max_it, bar_id);
@@ -1031,6 +1031,7 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ LayS scodes[DTL_MAX_SMEM_CODES];
     __shared__ __align__(8) uint64_t bars[W];
+    __shared__ int s_q[3];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     {
         int off = 0;
@@ -1041,6 +1042,7 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
             off += (int)lay_tab_bytes(g.n, g.m, g.lay_steps);
         }
         if (lane == 0) mbar_init(&bars[wid], 1);
+        if (threadIdx.x == 0) { s_q[0] = p.cnt[3]; s_q[1] = s_q[0] + p.cnt[5]; s_q[2] = s_q[1] + p.cnt[6]; }
         __syncthreads();
     }
     const int stg_bytes = p.cw_stride * 4 + DTL_STG_SLACK;
@@ -1054,7 +1056,7 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
     BpItem rec;
     rec.out_off = 0; rec.src = nullptr; rec.it = 0; rec.fec_id = 1; rec.k_ = 0; rec.shift = 0; rec.nbytes = 0; rec.len = 0;
     if (j < total) {
-        rec = p.items[j];
+        rec = p.items[bp_item_pos(s_q, j, p.cw_cap)];
         if (lane == 0) { mbar_expect_tx(bar, (uint32_t)rec.nbytes); bulk_g2s(stg, rec.src, (uint32_t)rec.nbytes, bar); }
     }
     uint32_t phase = 0;
@@ -1072,7 +1074,7 @@ __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
         nxt = __shfl_sync(0xffffffffu, nxt, 0);
         BpItem nrec = rec;
         if (nxt < total) {
-            nrec = p.items[nxt];
+            nrec = p.items[bp_item_pos(s_q, nxt, p.cw_cap)];
             if (lane == 0) { mbar_expect_tx(bar, (uint32_t)nrec.nbytes); bulk_g2s(stg, nrec.src, (uint32_t)nrec.nbytes, bar); }
         }
         const int nit = bp_lay_run(c, w, lane, p.max_it);
@@ -1366,7 +1368,7 @@ __global__ void __launch_bounds__(256) carry_sign_kernel(FecParams p)
 
 __global__ void fec_clear_kernel(int* cnt, unsigned long long* bits_used)
 {
-    cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; cnt[5] = cnt[6] = cnt[7] = 0;     // cnt[4] is the stand-alone decoder's cursor
+    cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; cnt[5] = cnt[6] = cnt[7] = 0; cnt[10] = 0;     // cnt[4] is the stand-alone decoder's cursor
     *bits_used = 0ull;
 }
 
