@@ -385,14 +385,15 @@ __global__ void __launch_bounds__(256) sync_cut_kernel(SyncParams p)
     // the oscillator's segments that can matter for this CTA's samples, in shared memory (a handful per call)
     __shared__ SyncSeg sseg[16];
     __shared__ int s_n;
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {                                     // the list is sorted by t: counting replaces searching
         const SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;
         const long long lo = t + q0, hi = t + min(q0 + 1024, FS) - 1;
-        int first = -1, n = 0;
-        for (int i = 0; i < nseg; i++) if (segs[i].t <= lo) first = i;        // the segment in force at the first sample
-        bool over = false;
-        for (int i = first < 0 ? 0 : first; i < nseg && segs[i].t <= hi; i++) { if (n < 16) sseg[n++] = segs[i]; else over = true; }
-        s_n = over ? -1 : n;                                    // more than 16 segments inside 1024 samples (a burst of false triggers): search the global list
+        int c_lo = 0, c_hi = 0;
+        for (int i = threadIdx.x; i < nseg; i += 32) { const long long ti = segs[i].t; c_lo += ti <= lo; c_hi += ti <= hi; }
+        c_lo = __reduce_add_sync(0xffffffffu, c_lo); c_hi = __reduce_add_sync(0xffffffffu, c_hi);
+        const int start = max(c_lo - 1, 0), n = c_hi - start;   // from the segment in force at the first sample to the last one that starts inside
+        for (int i = threadIdx.x; i < min(n, 16); i += 32) sseg[i] = segs[start + i];
+        if (threadIdx.x == 0) s_n = n > 16 ? -1 : n;            // more than 16 segments inside 1024 samples (a burst of false triggers): search the global list
     }
     __syncthreads();
     const int ns = s_n;
