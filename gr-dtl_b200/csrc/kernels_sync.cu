@@ -66,7 +66,13 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
     float* es = (float*)(sc + ncp);
     float* pe = es + ncp;
     float* se = pe + ncp;
-    for (int i = threadIdx.x; i < nx; i += blockDim.x) xs[i] = ld_w(w, p0 - N - W1 + i, base, len);
+    for (int i0 = threadIdx.x; i0 < nx; i0 += 4 * blockDim.x) {               // four loads in flight per thread
+        float2 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = i0 + u * blockDim.x; v[u] = i < nx ? ld_w(w, p0 - N - W1 + i, base, len) : make_float2(0.f, 0.f); }
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = i0 + u * blockDim.x; if (i < nx) xs[i] = v[u]; }
+    }
     __syncthreads();
     for (int i = threadIdx.x; i < nc; i += blockDim.x) {
         const float2 a = xs[i + W1], b = xs[i];                 // x[m], x[m - N/2], m = p0 - N + i
@@ -76,6 +82,38 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
     __syncthreads();
     // prefix (ascending) and suffix (descending) sums inside every aligned block: one thread per (block, direction) chain
     const int nb1 = nc / W1, nb2 = nc / W2;
+    if (NFIX == 64 && blockDim.x == 256) {
+        // fft_len 64: the same chains, laid out so that no warp mixes chain kinds and both directions run the same code (a
+        // per-thread step of +-1 element): the 34 E chains (64 long) on warps 0-1, the P chains as 136 chains of ONE float
+        // component (32 long) on warps 2-6.  The other threads wait at the barrier.
+        const int tid = threadIdx.x;
+        if (tid < 2 * nb2) {
+            const int dir = tid & 1, bb = tid >> 1, o = bb * 64 + 2 * bb;                 // PAD(bb * 64)
+            float* dst = dir ? se : pe;
+            float acc = 0.f;
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                const int at = o + (dir ? 63 - 32 * r + (1 - r) : 33 * r), step = dir ? -1 : 1;
+                const float* sp = es + at; float* dp = dst + at;
+                float v[32];
+#pragma unroll
+                for (int ii = 0; ii < 32; ii++) v[ii] = sp[step * ii];
+#pragma unroll
+                for (int ii = 0; ii < 32; ii++) { acc = (r == 0 && ii == 0) ? v[0] : __fadd_rn(acc, v[ii]); dp[step * ii] = acc; }
+            }
+        } else if (tid >= 64 && tid < 64 + 4 * nb1) {
+            const int c = tid - 64, comp = c & 1, dir = (c >> 1) & 1, bb = c >> 2;
+            const int at = 2 * (33 * bb + (dir ? 31 : 0)) + comp, step = dir ? -2 : 2;   // float index into the float2 arrays
+            const float* sp = (const float*)cs + at; float* dp = (float*)(dir ? sc : pc) + at;
+            float v[32];
+#pragma unroll
+            for (int ii = 0; ii < 32; ii++) v[ii] = sp[step * ii];
+            float acc = v[0];
+            dp[0] = acc;
+#pragma unroll
+            for (int ii = 1; ii < 32; ii++) { acc = __fadd_rn(acc, v[ii]); dp[step * ii] = acc; }
+        }
+    } else
     for (int b = threadIdx.x; b < 2 * (nb1 + nb2); b += blockDim.x) {
         const int dir = b & 1, bb = b >> 1;
         if (bb < nb1) {
