@@ -34,8 +34,14 @@ __global__ void __launch_bounds__(256) sync_append_kernel(SyncParams p)
     float2* dst = p.w_new + (size_t)s * p.w_cap;
     const float2* x = p.x + (size_t)s * p.T;
     const int keep = st.keep_len, total = keep + p.T;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
-        dst[i] = i < keep ? src[i] : __ldcs(&x[i - keep]);
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += 4 * stride) {       // four loads in flight per thread
+        float2 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = i0 + u * stride; if (i < total) v[u] = i < keep ? src[i] : __ldcs(&x[i - keep]); }
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const int i = i0 + u * stride; if (i < total) dst[i] = v[u]; }
+    }
 }
 
 // ---- Schmidl & Cox metric, one bit per position ------------------------------------------------------------------------
@@ -423,6 +429,11 @@ __global__ void __launch_bounds__(256) sync_cut_kernel(SyncParams p)
     // the oscillator's segments that can matter for this CTA's samples, in shared memory (a handful per call)
     __shared__ SyncSeg sseg[16];
     __shared__ int s_n;
+    // this thread's four delayed samples are requested before the segment search below: the two latencies overlap
+    const int qe = min(q0 + 1024, FS);
+    float2 yv[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) { const int q = q0 + threadIdx.x + 256 * u; yv[u] = q < qe ? ld_w(w, t + q - D, base, len) : make_float2(0.f, 0.f); }
     if (threadIdx.x < 32) {                                     // the list is sorted by t: counting replaces searching
         const SyncSeg* segs = p.segs + (size_t)s * p.seg_cap;
         const long long lo = t + q0, hi = t + min(q0 + 1024, FS) - 1;
@@ -436,8 +447,11 @@ __global__ void __launch_bounds__(256) sync_cut_kernel(SyncParams p)
     __syncthreads();
     const int ns = s_n;
     const double w0 = -2.0 / N, inv2pi = 0.15915494309189533577, twopi = 6.28318530717958647692;
-    for (int q = q0 + threadIdx.x; q < min(q0 + 1024, FS); q += blockDim.x) {
-        const float2 y = ld_w(w, t + q - D, base, len);
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int q = q0 + threadIdx.x + 256 * u;
+        if (q >= qe) break;
+        const float2 y = yv[u];
         const long long n = t + q;
         int k = -1;
         const SyncSeg* sl = sseg;
