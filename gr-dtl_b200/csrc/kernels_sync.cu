@@ -66,9 +66,10 @@ __global__ void __launch_bounds__(256) sync_metric_kernel(SyncParams p)
 #define PAD(i) ((i) + ((i) >> 5))
     float2* xs = (float2*)sm;                                   // x[p0 - N - W1 .. p0 + TILE)
     const int nx = TILE + N + W1, nc = TILE + N, ncp = PAD(nc) + 1;
-    float2* cs = xs + nx;                                       // c[p0 - N .. p0 + TILE), padded like the ones below
-    float2* pc = cs + ncp;
-    float2* sc = pc + ncp;
+    const int na = nx > ncp ? nx : ncp;
+    float2* cs = xs + na;                                       // c[p0 - N .. p0 + TILE), padded like the ones below
+    float2* pc = xs;                                            // the prefix sums take the samples' place (dead once c and e exist)
+    float2* sc = cs + ncp;
     float* es = (float*)(sc + ncp);
     float* pe = es + ncp;
     float* se = pe + ncp;
@@ -489,7 +490,8 @@ cudaError_t launch_sync_reset(cudaStream_t st, SyncState* state, int n)
 size_t sync_metric_smem(int N)
 {
     const int T = N > 1024 ? N : 1024, nc = T + N, ncp = nc + (nc >> 5) + 1;      // PAD of sync_metric_kernel
-    return (size_t)(T + N + N / 2) * 8 + 3 * (size_t)ncp * 8 + 3 * (size_t)ncp * 4 + 16;
+    const int nx = T + N + N / 2;
+    return (size_t)(nx > ncp ? nx : ncp) * 8 + 2 * (size_t)ncp * 8 + 3 * (size_t)ncp * 4 + 16;
 }
 
 cudaError_t launch_sync(cudaStream_t st, const SyncParams& p, int* launches)
