@@ -152,3 +152,43 @@ def test_two_code_handle_plain_decoder_matches_oracle():
         gb, gi = rx.ldpc_decode(fec, llr)
         assert np.array_equal(gb, ob) and np.array_equal(gi, oi) and oi.max() > 0
     rx.close()
+
+
+def test_fec_decode_device_llrs_at_any_alignment_and_row_stride():
+    """dtl_b200_fec_decode on DEVICE LLRs whose base is not 16-byte aligned and whose row stride is not a multiple of four
+    floats: the decoder fetches a queued codeword's run with ONE bulk copy of its 16-byte-aligned superset where that stays
+    inside the row and through the gathered block otherwise -- TB records and bytes equal the host-buffer call's (which equal
+    the oracle's, test above), for every lead-in 0..3."""
+    import torch
+    frame_len = 10
+    ocfg = make_oracle_cfg(frame_len=frame_len, alists=CODES)
+    rx = make_receiver(frame_len=frame_len, alists=CODES)
+    S, F = 12, 40
+    rng = np.random.default_rng(9)
+    fe = rng.integers(1, 3, size=S * F).astype(np.int32)
+    cn = np.full(S * F, 2, dtype=np.int32)
+    data, meta, o_llr, g_llr = _noisy_chain(ocfg, rx, S, F, cn, fe, 0.12, seed=21)
+    llr = o_llr[:, :rx.llr_stride].copy()
+    rx.reset(S)
+    ref = rx.fec_decode(llr, meta, S, F)
+    assert sum(int(ref["tbs"][s, :ref["ntbs"][s]]["avg_it"].sum()) for s in range(S)) > 0, "belief propagation never iterated"
+    tm = torch.from_numpy(meta.view(np.uint8).reshape(S * F, -1).copy()).cuda()
+    for front, extra in ((0, 0), (1, 1), (2, 3), (3, 2)):
+        w = rx.llr_stride + extra
+        buf = torch.full((front + S * F * w + 8,), float("nan"), dtype=torch.float32, device="cuda")
+        view = buf[front:front + S * F * w].view(S * F, w)
+        view[:, :rx.llr_stride] = torch.from_numpy(llr).cuda()
+        assert view.data_ptr() % 16 == (4 * front) % 16 and view.is_contiguous()
+        rx.reset(S)
+        got = rx.fec_decode(view, tm, S, F)
+        rx.sync()
+        nt = got["ntbs"].cpu().numpy()
+        nb = got["nbytes"].cpu().numpy()
+        assert np.array_equal(nt, ref["ntbs"]) and np.array_equal(nb, ref["nbytes"]), (front, extra)
+        from dtl_b200._capi import tb_result_dtype
+        tb = got["tbs"].cpu().numpy().view(tb_result_dtype).reshape(S, -1)
+        by = got["bytes"].cpu().numpy().reshape(S, -1)
+        for s in range(S):
+            assert tb[s, :nt[s]].tobytes() == ref["tbs"][s, :nt[s]].tobytes(), (front, extra, s)
+            assert np.array_equal(by[s, :nb[s]], ref["bytes"][s, :nb[s]]), (front, extra, s)
+    rx.close()
