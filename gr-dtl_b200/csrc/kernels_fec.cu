@@ -15,12 +15,15 @@
 //                           ranges of this call's frames) and one work item per codeword.
 //   2. ldpc_screen_kernel   bit-sliced syndrome check of every codeword's hard decisions, read from the SIGN WORDS the
 //                           equaliser kernel writes next to the LLRs (1 bit per LLR); clean codewords leave here, the others
-//                           are queued on four lists by a coarse syndrome weight, hardest first.
-//   3. bp_gather_kernel     the queued codewords' LLRs -> one contiguous, wire-order block each (segments, shortened
-//                           positions = -15 of tb_decoder.cc:145, sign flip of ldpc_dec.cc:64-66).
+//                           are queued on four lists by a coarse syndrome weight, hardest first, each with a record
+//                           (BpItem) of where its bits go and where its received run lies: a run inside one LLR row is
+//                           fetched IN PLACE by the decoder (the 16-byte-aligned superset of the run + a lead-in).
+//   3. bp_gather_kernel     only the queued codewords whose run straddles two segments (or is cut short): pieces and
+//                           defaults (shortened positions = -15 of tb_decoder.cc:145) -> one contiguous wire-order block.
 //   4. ldpc_bp_ref_kernel   (bp_ref.cuh; DTL_LDPC_REFERENCE) or ldpc_bp_lay_kernel (bp_layered.cuh; DTL_LDPC_LAYERED):
-//                           persistent grid, one codeword per warp from the queue, the NEXT codeword's block prefetched by a
-//                           TMA bulk copy; messages in shared memory; syndrome checks are warp votes, so a warp leaves as
+//                           persistent grid, one codeword per warp from the queue, the NEXT codeword's run prefetched by a
+//                           TMA bulk copy from the address in its record (sign flip of ldpc_dec.cc:64-66 on consumption);
+//                           messages in shared memory; syndrome checks are warp votes, so a warp leaves as
 //                           soon as its word converges.  (ldpc_bp_kernel below is the slot-major decoder of round 1, kept for
 //                           codes without a row-major instance and for A/B: DTL_BP_OLD=1.)
 //   5. tb_finish_kernel     one warp per TB: bits -> bytes LSB-first, mean iterations.
@@ -952,10 +955,12 @@ __device__ __forceinline__ size_t bp_item_pos(const int* q, int j, int cap)
 // queue.  What bounds this kernel is how many warps the SM can choose from, not instruction count: one warp issues an FP64
 // instruction with three register-pair operands about every six cycles however many independent chains it holds (tools/
 // div_bench.cu, tools/bp_bench.cu on a B200), the FP64 pipe takes one every two, and the shared memory a codeword needs
-// (11 KB) caps the codewords in flight at ~19 per SM -- so two warps share a codeword's rows and columns (the same total
-// warp-rounds: 148 rows = 32+32+32+32+20, 300 columns = 9 x 32 + 12) and 64 registers per thread keep 32 warps resident.
-// Each team owns a staging buffer and an mbarrier; the block of the NEXT codeword is fetched by one bulk copy
-// (cp.async.bulk -> mbarrier) as soon as the current one has been turned into likelihood ratios.
+// (11 KB) caps the codewords in flight at 19 per SM.  Default: NT = 32, ONE CTA of 19 warps per SM (the code tables staged
+// once).  NT = 64 (DTL_BP_TEAM=64: two warps share a codeword's rows and columns, 64 registers per thread keep 32 warps
+// resident) reaches the pipe's peak in the microbenchmark and loses in the kernel to spills in the division chains.
+// Each team owns a staging buffer and an mbarrier; the run of the NEXT codeword is fetched by one bulk copy
+// (cp.async.bulk -> mbarrier) from the address in its record (BpItem: the LLR row itself, or the gathered block) as soon as
+// the current one has been turned into likelihood ratios.
 template <int NT, int TEAMS, int MINB>
 __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams p)
 {
@@ -1023,7 +1028,7 @@ __global__ void __launch_bounds__(NT * TEAMS, MINB) ldpc_bp_ref_kernel(FecParams
     }
 }
 
-// Pass 2, layered mode (bp_layered.cuh): the same queue, gathered blocks and bulk-copy prefetch as ldpc_bp_ref_kernel, one
+// Pass 2, layered mode (bp_layered.cuh): the same queue, records and bulk-copy prefetch as ldpc_bp_ref_kernel, one
 // codeword per warp; the block's received values ARE the initial posteriors (no likelihood-ratio pass).
 template <int W, int MINB>
 __global__ void __launch_bounds__(32 * W, MINB) ldpc_bp_lay_kernel(FecParams p)
